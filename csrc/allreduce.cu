@@ -1,0 +1,398 @@
+// Fused DDP bucket collectives over NVLink 5 / NVSwitch peer memory.  sm_100a only.
+//
+// One kernel per bucket does what the reference's stack does in four steps
+// (/root/reference/ddp_gpus.py:32,38 -> torch Reducer: copy grads into a flat bucket scaled by
+// 1/world, ncclAllReduce, wait, copy the bucket back into .grad):
+//
+//   P0  gather  : read the scattered gradient tensors (pointer table), scale by 1/world, cast to
+//                 the wire dtype (fp32 or bf16) and write them into this rank's SYMMETRIC staging
+//                 buffer (peer-mapped on every GPU of the node);
+//   B1  barrier : per-CTA flags in the symmetric signal pads (release/acquire at system scope);
+//   P1  reduce  : one-shot  - every rank loads all peers' staging and sums (latency-optimal);
+//                 two-shot  - rank r sums sub-slice r of every chunk over all peers and stores the
+//                             result into every peer's staging (bandwidth-optimal, P2P only);
+//                 NVLS      - multimem.ld_reduce on sub-slice r (the switch adds), multimem.st of
+//                             the result to all ranks (the switch fans out);
+//   B2  barrier ; P2 scatter: staging -> the .grad tensors (fp32), i.e. no separate copy-back.
+//
+// CTA b of every rank owns the same chunks in every phase, so only CTA-local flags are needed and
+// the kernel never requires all CTAs to be co-resident.  Flags are consumed (1 -> 0) by the waiter,
+// so a slot can be reused by the next barrier without epochs.  Spins are bounded: on timeout the
+// kernel records it in *status and falls through, and the host raises.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+enum CollMode { kOneShot = 0, kTwoShot = 1, kNvls = 2, kBcast = 3 };
+
+struct CollTensor {
+  void* ptr;
+  long long numel;
+};
+struct CollChunk {
+  int tensor;        // index into the tensor table
+  int start;         // first element inside the tensor
+  int len;           // elements in this chunk
+  int pad_;
+  long long stage_off;   // element offset inside the staging region (multiple of 8)
+};
+
+struct CollArgs {
+  void* bufs[B200DT_MAX_WORLD];
+  uint32_t* sigs[B200DT_MAX_WORLD];
+  void* mc;
+  const CollTensor* tensors;
+  const CollChunk* chunks;
+  int n_chunks;
+  int rank, world, root;
+  long long stage_base;     // byte offset of the staging region inside each symmetric buffer
+  int tensor_bf16;          // dtype of the user tensors: 0 fp32, 1 bf16
+  int wire_bf16;            // dtype on the wire / in staging
+  float scale;
+  int sig_base;             // first signal word this launch may use
+  int* status;
+  unsigned long long spin_limit;
+};
+
+constexpr int kCollThreads = 512;
+
+__device__ __forceinline__ void block_barrier(const CollArgs& a) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < a.world) {
+    const int slot = a.sig_base + blockIdx.x * a.world;
+    uint32_t* remote = a.sigs[t] + slot + a.rank;
+    unsigned long long spins = 0;
+    while (cas_release_sys(remote, 0u, 1u) != 0u) {
+      if (++spins > a.spin_limit) { atomicExch(a.status, 1); break; }
+    }
+    uint32_t* local = a.sigs[a.rank] + slot + t;
+    spins = 0;
+    while (cas_acquire_sys(local, 1u, 0u) != 1u) {
+      if (++spins > a.spin_limit) { atomicExch(a.status, 2); break; }
+    }
+  }
+  __syncthreads();
+}
+
+// ---- 8-element group accessors -------------------------------------------------------------
+__device__ __forceinline__ void load8_tensor(const void* base, long long idx, int bf16, int n,
+                                             bool aligned, float (&f)[8]) {
+  if (bf16) {
+    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(base) + idx;
+    if (n == 8 && aligned) {
+      unpack8(ld_v4(p), f);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = j < n ? __bfloat162float(p[j]) : 0.f;
+    }
+  } else {
+    const float* p = reinterpret_cast<const float*>(base) + idx;
+    if (n == 8 && aligned) {
+      const uint4 a = ld_v4(p), b = ld_v4(p + 4);
+      f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y);
+      f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
+      f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y);
+      f[6] = __uint_as_float(b.z); f[7] = __uint_as_float(b.w);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = j < n ? p[j] : 0.f;
+    }
+  }
+}
+__device__ __forceinline__ void store8_tensor(void* base, long long idx, int bf16, int n,
+                                              bool aligned, const float (&f)[8]) {
+  if (bf16) {
+    __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(base) + idx;
+    if (n == 8 && aligned) {
+      st_v4(p, pack8(f));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j < n) p[j] = __float2bfloat16(f[j]);
+    }
+  } else {
+    float* p = reinterpret_cast<float*>(base) + idx;
+    if (n == 8 && aligned) {
+      st_v4(p, make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                          __float_as_uint(f[3])));
+      st_v4(p + 4, make_uint4(__float_as_uint(f[4]), __float_as_uint(f[5]), __float_as_uint(f[6]),
+                              __float_as_uint(f[7])));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j < n) p[j] = f[j];
+    }
+  }
+}
+// Staging is always 16-byte aligned and padded to 8 elements.
+__device__ __forceinline__ void load8_stage(const void* stage, long long e, int bf16, float (&f)[8]) {
+  if (bf16) {
+    unpack8(ld_sys_v4(reinterpret_cast<const __nv_bfloat16*>(stage) + e), f);
+  } else {
+    const float* p = reinterpret_cast<const float*>(stage) + e;
+    const uint4 a = ld_sys_v4(p), b = ld_sys_v4(p + 4);
+    f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y);
+    f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
+    f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y);
+    f[6] = __uint_as_float(b.z); f[7] = __uint_as_float(b.w);
+  }
+}
+__device__ __forceinline__ void store8_stage(void* stage, long long e, int bf16, const float (&f)[8]) {
+  if (bf16) {
+    st_v4(reinterpret_cast<__nv_bfloat16*>(stage) + e, pack8(f));
+  } else {
+    float* p = reinterpret_cast<float*>(stage) + e;
+    st_v4(p, make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                        __float_as_uint(f[3])));
+    st_v4(p + 4, make_uint4(__float_as_uint(f[4]), __float_as_uint(f[5]), __float_as_uint(f[6]),
+                            __float_as_uint(f[7])));
+  }
+}
+
+template <int kMode>
+__global__ void __launch_bounds__(kCollThreads)
+coll_kernel(const __grid_constant__ CollArgs a) {
+  const int esz_t = a.tensor_bf16 ? 2 : 4;
+  char* my_stage = reinterpret_cast<char*>(a.bufs[a.rank]) + a.stage_base;
+
+  // ---------------------------------------------------------------- P0: gather + scale + cast
+  if (kMode != kBcast || a.rank == a.root) {
+    for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
+      const CollChunk ch = a.chunks[c];
+      const CollTensor tt = a.tensors[ch.tensor];
+      const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
+      const int groups = (ch.len + 7) / 8;
+      for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+        float f[8];
+        const int n = min(8, ch.len - g * 8);
+        load8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] *= a.scale;
+        if (kMode == kBcast) {
+          // root pushes straight into every rank's staging (its own included)
+          if (a.mc != nullptr) {
+            // one multicast store fans out in the switch
+            char* dst = reinterpret_cast<char*>(a.mc) + a.stage_base;
+            if (a.wire_bf16) {
+              multimem_st_v4(reinterpret_cast<__nv_bfloat16*>(dst) + ch.stage_off + g * 8, pack8(f));
+            } else {
+              float* p = reinterpret_cast<float*>(dst) + ch.stage_off + g * 8;
+              multimem_st_v4(p, make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]),
+                                           __float_as_uint(f[2]), __float_as_uint(f[3])));
+              multimem_st_v4(p + 4, make_uint4(__float_as_uint(f[4]), __float_as_uint(f[5]),
+                                               __float_as_uint(f[6]), __float_as_uint(f[7])));
+            }
+          } else {
+            for (int r = 0; r < a.world; ++r)
+              store8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, ch.stage_off + g * 8,
+                           a.wire_bf16, f);
+          }
+        } else {
+          store8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f);
+        }
+      }
+    }
+  }
+  if (a.world > 1) block_barrier(a);
+
+  // ---------------------------------------------------------------- P1: reduce
+  if (kMode == kOneShot) {
+    // Reduce every chunk from all peers and write the result straight into the tensors.
+    for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
+      const CollChunk ch = a.chunks[c];
+      const CollTensor tt = a.tensors[ch.tensor];
+      const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
+      const int groups = (ch.len + 7) / 8;
+      for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        // Fixed summation order (rank 0..world-1) on every rank: results are bit-identical.
+        for (int r = 0; r < a.world; ++r) {
+          float f[8];
+          load8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, ch.stage_off + g * 8,
+                      a.wire_bf16, f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+        const int n = min(8, ch.len - g * 8);
+        store8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, acc);
+      }
+    }
+    // Peers may still be reading this rank's staging: hold the next writer back.
+    if (a.world > 1) block_barrier(a);
+    return;
+  }
+
+  if (kMode == kTwoShot || kMode == kNvls) {
+    for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
+      const CollChunk ch = a.chunks[c];
+      const int groups = (ch.len + 7) / 8;
+      const int per = (groups + a.world - 1) / a.world;      // groups owned by each rank
+      const int g0 = a.rank * per;
+      const int g1 = min(groups, g0 + per);
+      for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+        const long long e = ch.stage_off + (long long)g * 8;
+        if (kMode == kNvls) {
+          char* mcs = reinterpret_cast<char*>(a.mc) + a.stage_base;
+          if (a.wire_bf16) {
+            __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(mcs) + e;
+            const uint4 v = multimem_ld_reduce_bf16x8(p);
+            multimem_st_v4(p, v);
+          } else {
+            float* p = reinterpret_cast<float*>(mcs) + e;
+            const uint4 v0 = multimem_ld_reduce_f32x4(p);
+            const uint4 v1 = multimem_ld_reduce_f32x4(p + 4);
+            multimem_st_v4(p, v0);
+            multimem_st_v4(p + 4, v1);
+          }
+        } else {
+          float acc[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+          for (int r = 0; r < a.world; ++r) {
+            float f[8];
+            load8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, e, a.wire_bf16, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+          }
+          for (int r = 0; r < a.world; ++r) {
+            const int dst = (a.rank + r) % a.world;     // spread the writes over the links
+            store8_stage(reinterpret_cast<char*>(a.bufs[dst]) + a.stage_base, e, a.wire_bf16, acc);
+          }
+        }
+      }
+    }
+    if (a.world > 1) block_barrier(a);
+  }
+
+  // ---------------------------------------------------------------- P2: staging -> tensors
+  for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
+    const CollChunk ch = a.chunks[c];
+    const CollTensor tt = a.tensors[ch.tensor];
+    const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
+    const int groups = (ch.len + 7) / 8;
+    for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+      float f[8];
+      load8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f);
+      const int n = min(8, ch.len - g * 8);
+      store8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, f);
+    }
+  }
+  if (kMode == kBcast && a.world > 1) {
+    // root must not overwrite its peers' staging with the next broadcast before they drained it
+    block_barrier(a);
+  }
+}
+
+// Single-GPU emulation of the reduce arithmetic (tests without peers): out = scale * sum_r bufs[r].
+__global__ void emulate_kernel(const CollArgs a, void* out, long long n) {
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g * 8 < n;
+       g += (long long)gridDim.x * blockDim.x) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    const int cnt = (int)min(8LL, n - g * 8);
+    for (int r = 0; r < a.world; ++r) {
+      float f[8];
+      load8_tensor(a.bufs[r], g * 8, a.wire_bf16, cnt, true, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j] * a.scale;
+    }
+    store8_tensor(out, g * 8, a.wire_bf16, cnt, true, acc);
+  }
+}
+
+__global__ void scale_cast_kernel(const float* __restrict__ src, void* __restrict__ dst,
+                                  long long n, float scale, int dst_bf16) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float v = src[i] * scale;
+    if (dst_bf16) reinterpret_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16(v);
+    else reinterpret_cast<float*>(dst)[i] = v;
+  }
+}
+__global__ void cast_to_f32_kernel(const void* __restrict__ src, float* __restrict__ dst,
+                                   long long n, int src_bf16) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    dst[i] = src_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(src)[i])
+                      : reinterpret_cast<const float*>(src)[i];
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200dt_coll_chunk_bytes(void) { return (int)sizeof(CollChunk); }
+
+// mode: 0 one-shot all-reduce, 1 two-shot, 2 NVLS, 3 broadcast from `root`.
+// bufs / sigs: HOST arrays of `world` peer-mapped device pointers (symmetric buffer, signal pad).
+// tensors: device array of {ptr, numel}; chunks: device array of CollChunk (see
+// pytorch_distributed_training_tutorials_b200/ops/collectives.py for the builder).
+extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t* sigs, uint64_t mc,
+                                  int rank, int world, int root, const void* tensors,
+                                  const void* chunks, int n_chunks, long long stage_base_bytes,
+                                  int tensor_bf16, int wire_bf16, float scale, int sig_base,
+                                  int grid, int* status, void* stream) {
+  if (world < 1 || world > B200DT_MAX_WORLD || n_chunks <= 0) return world < 1 ? -3 : 0;
+  if (mode == kNvls && mc == 0) return -4;
+  if (grid < 1) grid = 1;
+  if (sig_base + grid * world > B200DT_SIGNAL_WORDS) return -5;
+  CollArgs a{};
+  for (int r = 0; r < world; ++r) {
+    a.bufs[r] = reinterpret_cast<void*>(bufs[r]);
+    a.sigs[r] = reinterpret_cast<uint32_t*>(sigs[r]);
+  }
+  a.mc = reinterpret_cast<void*>(mc);
+  a.tensors = reinterpret_cast<const CollTensor*>(tensors);
+  a.chunks = reinterpret_cast<const CollChunk*>(chunks);
+  a.n_chunks = n_chunks;
+  a.rank = rank; a.world = world; a.root = root;
+  a.stage_base = stage_base_bytes;
+  a.tensor_bf16 = tensor_bf16; a.wire_bf16 = wire_bf16 || tensor_bf16;
+  a.scale = scale; a.sig_base = sig_base; a.status = status;
+  a.spin_limit = 1ull << 26;     // ~ tens of seconds of polling before giving up
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (mode) {
+    case kOneShot: coll_kernel<kOneShot><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kTwoShot: coll_kernel<kTwoShot><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kNvls: coll_kernel<kNvls><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kBcast: coll_kernel<kBcast><<<grid, kCollThreads, 0, st>>>(a); break;
+    default: return -3;
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_allreduce_local_emulate(const uint64_t* bufs, int world, void* out,
+                                              long long n, int dtype, float scale, void* stream) {
+  if (world < 1 || world > B200DT_MAX_WORLD) return -3;
+  CollArgs a{};
+  for (int r = 0; r < world; ++r) a.bufs[r] = reinterpret_cast<void*>(bufs[r]);
+  a.world = world; a.wire_bf16 = dtype; a.scale = scale;
+  long long blocks = (n / 8 + 255) / 256 + 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  emulate_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a, out, n);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_scale_cast(const float* src, void* dst, long long n, float scale,
+                                 int dst_bf16, void* stream) {
+  if (n <= 0) return 0;
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  scale_cast_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, n, scale, dst_bf16);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_cast_to_f32(const void* src, float* dst, long long n, int src_bf16,
+                                  void* stream) {
+  if (n <= 0) return 0;
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  cast_to_f32_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, n, src_bf16);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,311 @@
+// BatchNorm (training) for NHWC bf16 activations, fused with ReLU and the residual add.
+// Replaces the cuDNN BatchNorm / ATen relu / add chain of torchvision's Bottleneck that the
+// reference runs in /root/reference/03.model_parallel.ipynb:807-833 (tv:models/resnet.py:108-163).
+//
+// Every kernel streams a [rows, C] matrix with 16-byte (8-channel) accesses.  A thread owns one
+// 8-channel group for its whole life, so per-channel constants live in registers; column sums are
+// kept in registers across a strip of rows, folded through shared memory and finished with one
+// fp32 atomic per channel per CTA.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+constexpr int kBnThreads = 256;
+
+struct Slab {
+  int cols_per_block;   // vector (8-channel) columns handled by one CTA
+  int rows_per_iter;    // rows covered by one CTA iteration
+  dim3 grid;
+};
+
+static Slab make_slab(long long rows, int C, int target_blocks) {
+  Slab s;
+  const int cv = C / 8;
+  s.cols_per_block = cv < 32 ? cv : 32;
+  // cols_per_block must divide 256 for the thread mapping below: C/8 in {8,16,32,...} does.
+  while (kBnThreads % s.cols_per_block) --s.cols_per_block;
+  s.rows_per_iter = kBnThreads / s.cols_per_block;
+  const int gx = (cv + s.cols_per_block - 1) / s.cols_per_block;
+  long long gy = target_blocks / gx;
+  const long long max_gy = (rows + s.rows_per_iter - 1) / s.rows_per_iter;
+  if (gy > max_gy) gy = max_gy;
+  if (gy < 1) gy = 1;
+  s.grid = dim3(gx, (unsigned)gy, 1);
+  return s;
+}
+
+// Fold per-thread accumulators acc[NACC][8] over the row-lanes of the CTA; thread row-lane 0
+// ends up with the CTA totals for its channel group.
+template <int NACC>
+__device__ __forceinline__ void fold_rows(float (&acc)[NACC][8], int tx, int ty, int cols,
+                                          int rowlanes, float* smem) {
+  // smem layout: [ty][NACC*8][cols]  (conflict-free: consecutive tx -> consecutive banks)
+  for (int a = 0; a < NACC; ++a)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) smem[(ty * NACC * 8 + a * 8 + j) * cols + tx] = acc[a][j];
+  __syncthreads();
+  if (ty == 0) {
+    for (int r = 1; r < rowlanes; ++r)
+      for (int a = 0; a < NACC; ++a)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[a][j] += smem[(r * NACC * 8 + a * 8 + j) * cols + tx];
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long rows, int C,
+                int cols, int rowlanes) {
+  extern __shared__ float smem[];
+  const int cv = C / 8;
+  const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
+  const int col = blockIdx.x * cols + tx;
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+  if (col < cv) {
+    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
+         r += (long long)gridDim.y * rowlanes) {
+      float f[8];
+      unpack8(ld_nc_v4(x + r * cv + col), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] += f[j] * f[j]; }
+    }
+  }
+  fold_rows<2>(acc, tx, ty, cols, rowlanes, smem);
+  if (ty == 0 && col < cv) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(sums + col * 8 + j, acc[0][j]);
+      atomicAdd(sums + C + col * 8 + j, acc[1][j]);
+    }
+  }
+}
+
+template <bool kTrain>
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint4* __restrict__ y,
+                const float* __restrict__ sums, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float* running_mean, float* running_var,
+                float* save_mean, float* save_invstd, const float* __restrict__ in_mean,
+                const float* __restrict__ in_var, long long rows, int C, float eps, float momentum,
+                int relu, int cols, int rowlanes) {
+  const int cv = C / 8;
+  const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
+  const int col = blockIdx.x * cols + tx;
+  if (col >= cv) return;
+  float scale[8], shift[8];
+  const float inv_rows = 1.f / (float)rows;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = col * 8 + j;
+    float mean, var;
+    if (kTrain) {
+      mean = sums[c] * inv_rows;
+      var = fmaxf(sums[C + c] * inv_rows - mean * mean, 0.f);
+    } else {
+      mean = in_mean[c];
+      var = in_var[c];
+    }
+    const float invstd = rsqrtf(var + eps);
+    scale[j] = gamma[c] * invstd;
+    shift[j] = beta[c] - mean * scale[j];
+    if (kTrain && blockIdx.y == 0 && ty == 0) {
+      save_mean[c] = mean;
+      save_invstd[c] = invstd;
+      if (running_mean != nullptr) {
+        const float unbiased = rows > 1 ? var * ((float)rows / (float)(rows - 1)) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+      }
+    }
+  }
+  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
+       r += (long long)gridDim.y * rowlanes) {
+    float f[8];
+    unpack8(ld_nc_v4(x + r * cv + col), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
+    if (res != nullptr) {
+      float g[8];
+      unpack8(ld_nc_v4(res + r * cv + col), g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += g[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    y[r * cv + col] = pack8(f);
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
+                     const uint4* __restrict__ x, const float* __restrict__ save_mean,
+                     const float* __restrict__ save_invstd, float* __restrict__ sums,
+                     uint4* __restrict__ dres, long long rows, int C, int relu, int cols,
+                     int rowlanes) {
+  extern __shared__ float smem[];
+  const int cv = C / 8;
+  const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
+  const int col = blockIdx.x * cols + tx;
+  float acc[2][8];
+  float mean[8], invstd[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    acc[0][j] = acc[1][j] = 0.f;
+    const int c = (col < cv ? col : 0) * 8 + j;
+    mean[j] = save_mean[c];
+    invstd[j] = save_invstd[c];
+  }
+  if (col < cv) {
+    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
+         r += (long long)gridDim.y * rowlanes) {
+      float g[8], xv[8];
+      unpack8(ld_nc_v4(dy + r * cv + col), g);
+      unpack8(ld_nc_v4(x + r * cv + col), xv);
+      if (relu) {
+        float yv[8];
+        unpack8(ld_nc_v4(y + r * cv + col), yv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      }
+      if (dres != nullptr) dres[r * cv + col] = pack8(g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        acc[0][j] += g[j];
+        acc[1][j] += g[j] * (xv[j] - mean[j]) * invstd[j];
+      }
+    }
+  }
+  fold_rows<2>(acc, tx, ty, cols, rowlanes, smem);
+  if (ty == 0 && col < cv) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(sums + col * 8 + j, acc[0][j]);
+      atomicAdd(sums + C + col * 8 + j, acc[1][j]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
+                    const uint4* __restrict__ x, const float* __restrict__ save_mean,
+                    const float* __restrict__ save_invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ sums, uint4* __restrict__ dx, float* dgamma,
+                    float* dbeta, long long rows, int C, int relu, int cols, int rowlanes) {
+  const int cv = C / 8;
+  const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
+  const int col = blockIdx.x * cols + tx;
+  if (col >= cv) return;
+  float mean[8], invstd[8], scale[8], mg[8], mgx[8];
+  const float inv_rows = 1.f / (float)rows;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = col * 8 + j;
+    mean[j] = save_mean[c];
+    invstd[j] = save_invstd[c];
+    scale[j] = gamma[c] * invstd[j];
+    mg[j] = sums[c] * inv_rows;
+    mgx[j] = sums[C + c] * inv_rows;
+    if (blockIdx.y == 0 && ty == 0) {
+      if (dbeta != nullptr) dbeta[c] = sums[c];
+      if (dgamma != nullptr) dgamma[c] = sums[C + c];
+    }
+  }
+  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
+       r += (long long)gridDim.y * rowlanes) {
+    float g[8], xv[8];
+    unpack8(ld_nc_v4(dy + r * cv + col), g);
+    unpack8(ld_nc_v4(x + r * cv + col), xv);
+    if (relu) {
+      float yv[8];
+      unpack8(ld_nc_v4(y + r * cv + col), yv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xhat = (xv[j] - mean[j]) * invstd[j];
+      g[j] = scale[j] * (g[j] - mg[j] - xhat * mgx[j]);
+    }
+    dx[r * cv + col] = pack8(g);
+  }
+}
+
+static int target_blocks() { return 148 * 6; }
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream) {
+  if (C % 8 || rows <= 0) return -3;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+  if (e != cudaSuccess) return (int)e;
+  Slab s = make_slab(rows, C, target_blocks());
+  const size_t smem = sizeof(float) * kBnThreads * 16;
+  bn_stats_kernel<<<s.grid, kBnThreads, smem, st>>>(reinterpret_cast<const uint4*>(x), sums, rows, C,
+                                                    s.cols_per_block, s.rows_per_iter);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_bn_apply(const void* x, const void* residual, void* y, const float* sums,
+                               const float* gamma, const float* beta, float* running_mean,
+                               float* running_var, float* save_mean, float* save_invstd,
+                               long long rows, int C, float eps, float momentum, int relu,
+                               void* stream) {
+  if (C % 8 || rows <= 0) return -3;
+  Slab s = make_slab(rows, C, target_blocks());
+  bn_apply_kernel<true><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
+      reinterpret_cast<uint4*>(y), sums, gamma, beta, running_mean, running_var, save_mean,
+      save_invstd, nullptr, nullptr, rows, C, eps, momentum, relu, s.cols_per_block,
+      s.rows_per_iter);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y,
+                                    const float* gamma, const float* beta, const float* mean,
+                                    const float* var, long long rows, int C, float eps, int relu,
+                                    void* stream) {
+  if (C % 8 || rows <= 0) return -3;
+  Slab s = make_slab(rows, C, target_blocks());
+  bn_apply_kernel<false><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
+      reinterpret_cast<uint4*>(y), nullptr, gamma, beta, nullptr, nullptr, nullptr, nullptr, mean,
+      var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x,
+                                    const float* save_mean, const float* save_invstd, float* sums,
+                                    void* dres, long long rows, int C, int relu, void* stream) {
+  if (C % 8 || rows <= 0) return -3;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+  if (e != cudaSuccess) return (int)e;
+  Slab s = make_slab(rows, C, target_blocks());
+  const size_t smem = sizeof(float) * kBnThreads * 16;
+  bn_bwd_reduce_kernel<<<s.grid, kBnThreads, smem, st>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
+      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, sums,
+      reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x,
+                                   const float* save_mean, const float* save_invstd,
+                                   const float* gamma, const float* sums, void* dx, float* dgamma,
+                                   float* dbeta, long long rows, int C, int relu, void* stream) {
+  if (C % 8 || rows <= 0) return -3;
+  Slab s = make_slab(rows, C, target_blocks());
+  bn_bwd_apply_kernel<<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
+      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, sums,
+      reinterpret_cast<uint4*>(dx), dgamma, dbeta, rows, C, relu, s.cols_per_block, s.rows_per_iter);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,770 @@
+// Tiled-pixel implicit GEMM on tcgen05 / TMEM, fed by TMA.  sm_100a only.
+//
+// One persistent, warp-specialised kernel serves every GEMM-shaped op of the library:
+//   * Linear forward / dgrad           (A = rows x K, K-major;  B = weights, K-major)
+//   * Conv2d forward / dgrad, NHWC     (A = pixel boxes fetched by 4-D TMA with the filter-tap
+//                                        offset folded into the box origin; padding = TMA
+//                                        out-of-bounds zero fill; stride 2 = phase views)
+//   * Linear / Conv2d weight gradient  (both operands MN-major, reduction over pixels,
+//                                        split-K across CTAs with fp32 red.add)
+//
+// Roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (+TMEM
+// allocation), warps 2..5 = epilogue (tcgen05.ld -> registers -> global).  Two TMEM accumulator
+// stages let the epilogue of tile i overlap the main loop of tile i+1.
+//
+// Replaces what the reference reaches through cuBLAS / cuDNN: nn.Linear
+// (/root/reference/ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)
+// and the torchvision ResNet-50 convolutions (03.model_parallel.ipynb:807-833).
+#include "ptx.cuh"
+#include "common.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+constexpr int kBM = 128;          // UMMA M (cta_group::1)
+constexpr int kBK = 64;           // K elements per stage (one 128-byte swizzle row)
+constexpr int kThreads = 192;
+constexpr int kMaxTaps = 9;
+constexpr int kMaxMaps = 4;
+
+struct Tap {
+  int8_t map, dw, dh, pad;
+};
+
+struct GemmParams {
+  int kind;                 // 0 = FPROP-like (A pixels x K), 1 = WGRAD-like (reduce over pixels)
+  int BN;                   // UMMA N: 64, 128 or 256 (multiple of 64)
+  int stages;
+  int tiles_m, tiles_n, splits;
+  int kb_total, kb_per_split;
+  // pixel tiling of the A operand (FPROP) / of the reduction (WGRAD)
+  int bw, bh, bn;           // box extents; bw*bh*bn == 128 (FPROP) or 64 (WGRAD)
+  int tiles_w, tiles_h;     // boxes per row / per column of one image
+  int W, H, NB;             // valid extents for masking
+  int cin_blocks;           // FPROP: Cin / 64 ; WGRAD: N tiles per tap
+  int ntaps;
+  Tap taps[kMaxTaps];
+  // epilogue
+  void* C;
+  long long sN, sH, sW;     // FPROP: element strides of an output pixel; WGRAD: sW = ldc
+  int n_valid;              // valid output columns
+  int m_valid;              // WGRAD: valid output rows (Cout)
+  int out_fp32, relu, atomic;
+  const float* bias;
+};
+
+struct alignas(8) Barriers {
+  uint64_t full[8];
+  uint64_t empty[8];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ void store_chunk(const GemmParams& p, const float (&f)[32],
+                                            long long row_off, int col0, bool row_ok) {
+  if (!row_ok) return;
+  const int nrem = p.n_valid - col0;
+  if (nrem <= 0) return;
+  if (p.out_fp32) {
+    float* dst = reinterpret_cast<float*>(p.C) + row_off + col0;
+    if (p.atomic) {
+      if (nrem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(f[j]),
+                       "f"(f[j + 1]), "f"(f[j + 2]), "f"(f[j + 3])
+                       : "memory");
+      } else {
+        for (int j = 0; j < 32 && j < nrem; ++j) atomicAdd(dst + j, f[j]);
+      }
+    } else if (nrem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(dst + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+    } else {
+      for (int j = 0; j < 32 && j < nrem; ++j) dst[j] = f[j];
+    }
+  } else {
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + row_off + col0;
+    if (nrem >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        uint4 u;
+        u.x = pack_bf16x2(f[j], f[j + 1]);
+        u.y = pack_bf16x2(f[j + 2], f[j + 3]);
+        u.z = pack_bf16x2(f[j + 4], f[j + 5]);
+        u.w = pack_bf16x2(f[j + 6], f[j + 7]);
+        *reinterpret_cast<uint4*>(dst + j) = u;
+      }
+    } else {
+      for (int j = 0; j < 32 && j < nrem; ++j) dst[j] = __float2bfloat16(f[j]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+               const __grid_constant__ CUtensorMap mapA2, const __grid_constant__ CUtensorMap mapA3,
+               const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
+               const __grid_constant__ CUtensorMap mapB2, const __grid_constant__ CUtensorMap mapB3,
+               const __grid_constant__ GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128-byte swizzle atoms.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int a_stage_bytes = kBM * kBK * 2;            // 16 KB
+  const int b_stage_bytes = p.BN * kBK * 2;           // 8..32 KB
+  const int stage_bytes = a_stage_bytes + b_stage_bytes;
+  Barriers* bars = reinterpret_cast<Barriers*>(smem + p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mapA0);
+    tma_prefetch_desc(&mapB0);
+    for (int i = 0; i < p.stages; ++i) {
+      mbar_init(&bars->full[i], 1);
+      mbar_init(&bars->empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->tmem_full[i], 1);
+      mbar_init(&bars->tmem_empty[i], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc<512>(&bars->tmem_base);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      const CUtensorMap* mapsA[kMaxMaps] = {&mapA0, &mapA1, &mapA2, &mapA3};
+      const CUtensorMap* mapsB[kMaxMaps] = {&mapB0, &mapB1, &mapB2, &mapB3};
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int n_blk = t % p.tiles_n;
+        const int m_blk = (t / p.tiles_n) % p.tiles_m;
+        const int split = t / (p.tiles_n * p.tiles_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        if (p.kind == 0) {
+          const int tw = m_blk % p.tiles_w;
+          const int th = (m_blk / p.tiles_w) % p.tiles_h;
+          const int tn = m_blk / (p.tiles_w * p.tiles_h);
+          const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+          for (int kb = kb0; kb < kb1; ++kb) {
+            const int tap = kb / p.cin_blocks;
+            const int cb = kb - tap * p.cin_blocks;
+            const Tap tp = p.taps[tap];
+            mbar_wait(&bars->empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * stage_bytes;
+            uint8_t* sb = sa + a_stage_bytes;
+            mbar_expect_tx(&bars->full[stage], stage_bytes);
+            tma_load_4d(sa, mapsA[tp.map], &bars->full[stage], cb * kBK, w0 + tp.dw, h0 + tp.dh, n0);
+            tma_load_2d(sb, mapsB[0], &bars->full[stage], kb * kBK, n_blk * p.BN);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        } else {
+          const int tap = n_blk / p.cin_blocks;
+          const int ct = n_blk - tap * p.cin_blocks;
+          const Tap tp = p.taps[tap];
+          const int nchunks_b = p.BN / 64;
+          for (int kb = kb0; kb < kb1; ++kb) {
+            const int tw = kb % p.tiles_w;
+            const int th = (kb / p.tiles_w) % p.tiles_h;
+            const int tn = kb / (p.tiles_w * p.tiles_h);
+            const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+            mbar_wait(&bars->empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * stage_bytes;
+            uint8_t* sb = sa + a_stage_bytes;
+            mbar_expect_tx(&bars->full[stage], stage_bytes);
+            // A = dY^T : two 64-wide chunks of output channels, 64 pixels deep.
+            tma_load_4d(sa, mapsA[0], &bars->full[stage], m_blk * kBM, w0, h0, n0);
+            tma_load_4d(sa + 8192, mapsA[0], &bars->full[stage], m_blk * kBM + 64, w0, h0, n0);
+            for (int c = 0; c < nchunks_b; ++c)
+              tma_load_4d(sb + c * 8192, mapsB[tp.map], &bars->full[stage],
+                          ct * p.BN + c * 64, w0 + tp.dw, h0 + tp.dh, n0);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const bool mn = p.kind == 1;
+      const uint32_t idesc = umma_idesc_bf16(kBM, p.BN, mn, mn);
+      const uint32_t lbo = mn ? 8192u : 16u;
+      const uint32_t kstep = mn ? 2048u : 32u;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / (p.tiles_n * p.tiles_m);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * p.BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&bars->full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint32_t sb = sa + a_stage_bytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = umma_desc_sw128(sa + k * kstep, lbo, 1024);
+            const uint64_t db = umma_desc_sw128(sb + k * kstep, lbo, 1024);
+            umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&bars->empty[stage]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&bars->tmem_full[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue
+    const int q = warp & 3;                // TMEM lane quarter this warp may touch
+    const int row = q * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int n_blk = t % p.tiles_n;
+      const int m_blk = (t / p.tiles_n) % p.tiles_m;
+      bool row_ok;
+      long long row_off;
+      int col_base;
+      if (p.kind == 0) {
+        const int tw = m_blk % p.tiles_w;
+        const int th = (m_blk / p.tiles_w) % p.tiles_h;
+        const int tn = m_blk / (p.tiles_w * p.tiles_h);
+        const int dw = row % p.bw;
+        const int dh = (row / p.bw) % p.bh;
+        const int dn = row / (p.bw * p.bh);
+        const int w = tw * p.bw + dw, h = th * p.bh + dh, n = tn * p.bn + dn;
+        row_ok = (w < p.W) && (h < p.H) && (n < p.NB);
+        row_off = n * p.sN + h * p.sH + w * p.sW;
+        col_base = n_blk * p.BN;
+      } else {
+        const int r = m_blk * kBM + row;
+        row_ok = r < p.m_valid;
+        row_off = static_cast<long long>(r) * p.sW;
+        col_base = n_blk * p.BN;     // taps are laid out consecutively: tap * Cin + ct * BN
+      }
+      mbar_wait(&bars->tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * p.BN;
+      for (int c = 0; c < p.BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c * 32, v);
+        tmem_ld_wait();
+        float f[32];
+        const int col0 = col_base + c * 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.n_valid) f[j] += __ldg(p.bias + col0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        store_chunk(p, f, row_off, col0, row_ok);
+      }
+      tc_fence_before();
+      mbar_arrive(&bars->tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Host side: tensor-map construction and launch.
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  return fn;
+}
+
+// dims: innermost first (C, W, H, N); strides in ELEMENTS for W, H, N.
+static int make_map4(CUtensorMap* m, const void* base, const long long dims[4],
+                     const long long strides_el[3], const int box[4]) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return -1;
+  cuuint64_t gd[4] = {(cuuint64_t)dims[0], (cuuint64_t)dims[1], (cuuint64_t)dims[2],
+                      (cuuint64_t)dims[3]};
+  cuuint64_t gs[3] = {(cuuint64_t)strides_el[0] * 2, (cuuint64_t)strides_el[1] * 2,
+                      (cuuint64_t)strides_el[2] * 2};
+  cuuint32_t bx[4] = {(cuuint32_t)box[0], (cuuint32_t)box[1], (cuuint32_t)box[2],
+                      (cuuint32_t)box[3]};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
+}
+
+static int make_map2(CUtensorMap* m, const void* base, long long inner, long long outer,
+                     long long ld_el, int box_inner, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return -1;
+  cuuint64_t gd[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t gs[1] = {(cuuint64_t)ld_el * 2};
+  cuuint32_t bx[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
+                  GemmParams& p, cudaStream_t stream) {
+  const int stage_bytes = kBM * kBK * 2 + p.BN * kBK * 2;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) return -2;
+  p.stages = stages;
+  const int smem = stages * stage_bytes + (int)sizeof(Barriers) + 1024;
+  static int configured = 0;
+  if (configured < smem) {
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         227 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    configured = 227 * 1024;
+  }
+  const int total = p.tiles_m * p.tiles_n * p.splits;
+  int grid = total < num_sms() ? total : num_sms();
+  if (grid <= 0) return 0;
+  tc_gemm_kernel<<<grid, kThreads, smem, stream>>>(mapsA[0], mapsA[1], mapsA[2], mapsA[3], mapsB[0],
+                                                   mapsB[1], mapsB[2], mapsB[3], p);
+  return (int)cudaGetLastError();
+}
+
+static int pick_bn(int n) {
+  if (n % 256 == 0 || n > 512) return 256;
+  if (n % 128 == 0 || n > 128) return 128;
+  return 64;
+}
+
+// Pixel box (bw, bh, bn) with bw | W, bh | H and bw*bh*bn == target (128 or 64); prefers the
+// widest spatial footprint so that neighbouring taps re-hit the same L2 lines.
+static void pick_box(int W, int H, int target, int* bw, int* bh, int* bn) {
+  int best_w = 1, best_h = 1;
+  for (int w = 1; w <= W && w <= target; ++w) {
+    if (W % w) continue;
+    for (int h = 1; h <= H && w * h <= target; ++h) {
+      if (H % h) continue;
+      if (target % (w * h)) continue;
+      if (w * h > best_w * best_h) { best_w = w; best_h = h; }
+    }
+  }
+  *bw = best_w;
+  *bh = best_h;
+  *bn = target / (best_w * best_h);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// C[M,N] (bf16 or fp32) = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU)     -- all row-major, bf16 inputs.
+extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                                   int lda, int ldb, int ldc, const float* bias, int relu,
+                                   int out_fp32, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((lda % 8) || (ldb % 8) || (K % 8)) return -3;
+  GemmParams p{};
+  p.kind = 0;
+  p.BN = pick_bn(N);
+  p.tiles_m = (M + kBM - 1) / kBM;
+  p.tiles_n = (N + p.BN - 1) / p.BN;
+  p.splits = 1;
+  p.kb_total = (K + kBK - 1) / kBK;
+  p.kb_per_split = p.kb_total;
+  p.bw = 128; p.bh = 1; p.bn = 1;
+  p.tiles_w = p.tiles_m; p.tiles_h = 1;
+  p.W = M; p.H = 1; p.NB = 1;
+  p.cin_blocks = p.kb_total;
+  p.ntaps = 1;
+  p.taps[0] = Tap{0, 0, 0, 0};
+  p.C = C; p.sN = 0; p.sH = 0; p.sW = ldc;
+  p.n_valid = N; p.m_valid = M;
+  p.out_fp32 = out_fp32; p.relu = relu; p.atomic = 0; p.bias = bias;
+  CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+  long long dims[4] = {K, M, 1, 1};
+  long long str[3] = {lda, (long long)lda * M, (long long)lda * M};
+  int box[4] = {kBK, 128, 1, 1};
+  int r = make_map4(&ma[0], A, dims, str, box);
+  if (r) return r;
+  ma[1] = ma[2] = ma[3] = ma[0];
+  r = make_map2(&mb[0], B, K, N, ldb, kBK, p.BN);
+  if (r) return r;
+  mb[1] = mb[2] = mb[3] = mb[0];
+  return launch(ma, mb, p, (cudaStream_t)stream);
+}
+
+// C[M,N] fp32 (+)= A[Kr,M]^T * B[Kr,N]   (reduction over the Kr rows; both operands row-major
+// with the reduction index outermost, i.e. MN-major).  Used for weight gradients:
+// dW[Cout,Cin] = dY[rows,Cout]^T * X[rows,Cin].  C must be zero-filled by the caller when
+// `splits` > 1 (the kernel accumulates with red.add); pass splits = 0 to let the library choose,
+// in which case C is cleared here.
+extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C, int M, int N,
+                                          int Kr, int lda, int ldb, int ldc, int splits,
+                                          void* stream) {
+  if (M <= 0 || N <= 0 || Kr <= 0) return 0;
+  if ((lda % 8) || (ldb % 8)) return -3;
+  GemmParams p{};
+  p.kind = 1;
+  p.BN = (N > 64) ? 128 : 64;
+  p.tiles_m = (M + kBM - 1) / kBM;
+  p.tiles_n = (N + p.BN - 1) / p.BN;
+  p.kb_total = (Kr + 63) / 64;
+  const int out_tiles = p.tiles_m * p.tiles_n;
+  bool clear = false;
+  if (splits <= 0) {
+    splits = (2 * num_sms() + out_tiles - 1) / out_tiles;
+    if (splits > p.kb_total) splits = p.kb_total;
+    if (splits < 1) splits = 1;
+    clear = splits > 1;
+  }
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.bw = 64; p.bh = 1; p.bn = 1;
+  p.tiles_w = p.kb_total; p.tiles_h = 1;
+  p.W = Kr; p.H = 1; p.NB = 1;
+  p.cin_blocks = p.tiles_n;
+  p.ntaps = 1;
+  p.taps[0] = Tap{0, 0, 0, 0};
+  p.C = C; p.sW = ldc; p.n_valid = N; p.m_valid = M;
+  p.out_fp32 = 1; p.relu = 0; p.atomic = p.splits > 1; p.bias = nullptr;
+  if (clear) {
+    cudaError_t e = cudaMemsetAsync(C, 0, sizeof(float) * (size_t)ldc * M, (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+  long long dimsA[4] = {M, Kr, 1, 1};
+  long long strA[3] = {lda, (long long)lda * Kr, (long long)lda * Kr};
+  int box[4] = {64, 64, 1, 1};
+  int r = make_map4(&ma[0], A, dimsA, strA, box);
+  if (r) return r;
+  ma[1] = ma[2] = ma[3] = ma[0];
+  long long dimsB[4] = {N, Kr, 1, 1};
+  long long strB[3] = {ldb, (long long)ldb * Kr, (long long)ldb * Kr};
+  r = make_map4(&mb[0], B, dimsB, strB, box);
+  if (r) return r;
+  mb[1] = mb[2] = mb[3] = mb[0];
+  return launch(ma, mb, p, (cudaStream_t)stream);
+}
+
+// NHWC conv2d forward as implicit GEMM.  x: [NB, H, W, Cin] bf16, w: [Cout, R, S, Cin] bf16,
+// y: [NB, Ho, Wo, Cout] bf16.  Square filters R = S in {1, 3}, pad = R/2, stride in {1, 2},
+// Cin % 64 == 0.  For stride 2, H and W must be even.
+extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, int NB, int H, int W,
+                                        int Cin, int Cout, int R, int stride, int relu,
+                                        void* stream) {
+  if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cin % 64) || (Cout % 8)) return -3;
+  if (stride == 2 && ((H | W) & 1)) return -3;
+  const int Ho = H / stride, Wo = W / stride;
+  GemmParams p{};
+  p.kind = 0;
+  p.BN = pick_bn(Cout);
+  pick_box(Wo, Ho, 128, &p.bw, &p.bh, &p.bn);
+  p.tiles_w = Wo / p.bw;
+  p.tiles_h = Ho / p.bh;
+  const int tiles_nb = (NB + p.bn - 1) / p.bn;
+  p.tiles_m = p.tiles_w * p.tiles_h * tiles_nb;
+  p.tiles_n = (Cout + p.BN - 1) / p.BN;
+  p.splits = 1;
+  p.cin_blocks = Cin / 64;
+  p.ntaps = R * R;
+  p.kb_total = p.ntaps * p.cin_blocks;
+  p.kb_per_split = p.kb_total;
+  p.W = Wo; p.H = Ho; p.NB = NB;
+  p.C = y;
+  p.sW = Cout; p.sH = (long long)Wo * Cout; p.sN = (long long)Ho * Wo * Cout;
+  p.n_valid = Cout; p.m_valid = 0;
+  p.out_fp32 = 0; p.relu = relu; p.atomic = 0; p.bias = nullptr;
+  CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  int box[4] = {64, p.bw, p.bh, p.bn};
+  int r;
+  if (stride == 1) {
+    long long dims[4] = {Cin, W, H, NB};
+    long long str[3] = {Cin, (long long)W * Cin, (long long)H * W * Cin};
+    r = make_map4(&ma[0], xb, dims, str, box);
+    if (r) return r;
+    ma[1] = ma[2] = ma[3] = ma[0];
+    const int pad = R / 2;
+    for (int rr = 0; rr < R; ++rr)
+      for (int ss = 0; ss < R; ++ss)
+        p.taps[rr * R + ss] = Tap{0, (int8_t)(ss - pad), (int8_t)(rr - pad), 0};
+  } else {
+    // Input pixel (2h + dy, 2w + dx) lives in phase view (dy & 1, dx & 1) at (h + dy>>1, w + dx>>1).
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        long long dims[4] = {Cin, W / 2, H / 2, NB};
+        long long str[3] = {2LL * Cin, 2LL * W * Cin, (long long)H * W * Cin};
+        r = make_map4(&ma[py * 2 + px], xb + ((long long)py * W + px) * Cin, dims, str, box);
+        if (r) return r;
+      }
+    const int pad = R / 2;
+    for (int rr = 0; rr < R; ++rr)
+      for (int ss = 0; ss < R; ++ss) {
+        const int dy = rr - pad, dx = ss - pad;
+        const int py = dy & 1, px = dx & 1;
+        p.taps[rr * R + ss] =
+            Tap{(int8_t)(py * 2 + px), (int8_t)((dx - px) / 2), (int8_t)((dy - py) / 2), 0};
+      }
+  }
+  r = make_map2(&mb[0], w, (long long)p.ntaps * Cin, Cout, (long long)p.ntaps * Cin, kBK, p.BN);
+  if (r) return r;
+  mb[1] = mb[2] = mb[3] = mb[0];
+  return launch(ma, mb, p, (cudaStream_t)stream);
+}
+
+// NHWC conv2d weight gradient.  x: [NB,H,W,Cin], dy: [NB,Ho,Wo,Cout] (bf16), dw: [Cout,R,S,Cin] fp32
+// (overwritten).  Same shape constraints as the forward; additionally Cout % 64 == 0.
+extern "C" int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int NB, int H,
+                                        int W, int Cin, int Cout, int R, int stride,
+                                        void* stream) {
+  if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cin % 64) || (Cout % 64)) return -3;
+  if (stride == 2 && ((H | W) & 1)) return -3;
+  const int Ho = H / stride, Wo = W / stride;
+  GemmParams p{};
+  p.kind = 1;
+  p.BN = (Cin % 128 == 0) ? 128 : 64;
+  pick_box(Wo, Ho, 64, &p.bw, &p.bh, &p.bn);
+  p.tiles_w = Wo / p.bw;
+  p.tiles_h = Ho / p.bh;
+  const int tiles_nb = (NB + p.bn - 1) / p.bn;
+  p.kb_total = p.tiles_w * p.tiles_h * tiles_nb;
+  p.ntaps = R * R;
+  p.cin_blocks = Cin / p.BN;
+  p.tiles_m = (Cout + kBM - 1) / kBM;
+  p.tiles_n = p.ntaps * p.cin_blocks;
+  const int out_tiles = p.tiles_m * p.tiles_n;
+  int splits = (2 * num_sms() + out_tiles - 1) / out_tiles;
+  if (splits > p.kb_total) splits = p.kb_total;
+  if (splits < 1) splits = 1;
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.W = Wo; p.H = Ho; p.NB = NB;
+  p.C = dw; p.sW = (long long)p.ntaps * Cin; p.n_valid = p.ntaps * Cin; p.m_valid = Cout;
+  p.out_fp32 = 1; p.relu = 0; p.atomic = p.splits > 1; p.bias = nullptr;
+  if (p.atomic) {
+    cudaError_t e = cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)Cout * p.ntaps * Cin,
+                                    (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+  int box[4] = {64, p.bw, p.bh, p.bn};
+  long long dimsA[4] = {Cout, Wo, Ho, NB};
+  long long strA[3] = {Cout, (long long)Wo * Cout, (long long)Ho * Wo * Cout};
+  int r = make_map4(&ma[0], dy, dimsA, strA, box);
+  if (r) return r;
+  ma[1] = ma[2] = ma[3] = ma[0];
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+  const int pad = R / 2;
+  if (stride == 1) {
+    long long dims[4] = {Cin, W, H, NB};
+    long long str[3] = {Cin, (long long)W * Cin, (long long)H * W * Cin};
+    r = make_map4(&mb[0], xb, dims, str, box);
+    if (r) return r;
+    mb[1] = mb[2] = mb[3] = mb[0];
+    for (int rr = 0; rr < R; ++rr)
+      for (int ss = 0; ss < R; ++ss)
+        p.taps[rr * R + ss] = Tap{0, (int8_t)(ss - pad), (int8_t)(rr - pad), 0};
+  } else {
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        long long dims[4] = {Cin, W / 2, H / 2, NB};
+        long long str[3] = {2LL * Cin, 2LL * W * Cin, (long long)H * W * Cin};
+        r = make_map4(&mb[py * 2 + px], xb + ((long long)py * W + px) * Cin, dims, str, box);
+        if (r) return r;
+      }
+    for (int rr = 0; rr < R; ++rr)
+      for (int ss = 0; ss < R; ++ss) {
+        const int dy_ = rr - pad, dx_ = ss - pad;
+        const int py = dy_ & 1, px = dx_ & 1;
+        p.taps[rr * R + ss] =
+            Tap{(int8_t)(py * 2 + px), (int8_t)((dx_ - px) / 2), (int8_t)((dy_ - py) / 2), 0};
+      }
+  }
+  return launch(ma, mb, p, (cudaStream_t)stream);
+}
+
+// Zero one phase view of a NHWC tensor (used when no filter tap reaches that phase).
+__global__ void zero_phase_kernel(__nv_bfloat16* base, int NB, int Ho, int Wo, int C, long long sN,
+                                  long long sH, long long sW) {
+  const long long total = (long long)NB * Ho * Wo * (C / 8);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (C / 8));
+    long long pix = i / (C / 8);
+    const int w = (int)(pix % Wo); pix /= Wo;
+    const int h = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    *reinterpret_cast<uint4*>(base + n * sN + h * sH + w * sW + c8 * 8) = make_uint4(0, 0, 0, 0);
+  }
+}
+
+// NHWC conv2d data gradient.  dy: [NB,Ho,Wo,Cout] bf16, dx: [NB,H,W,Cin] bf16 (fully overwritten).
+// `wt` is the per-phase transposed filter produced by b200dt_filter_transpose_bf16:
+// for every output phase (py, px) in [0,stride)^2, in that order, the taps (rr, ss) (row-major
+// order) with (py + pad - rr) % stride == 0 and (px + pad - ss) % stride == 0 are stored as
+// wt_phase[Cin][tap][Cout] = w[Cout][rr][ss][Cin].  Then
+//   dx(s*i + py, s*j + px) = sum_taps dy(i + (py + pad - rr)/s, j + (px + pad - ss)/s) * w[., rr, ss, .]
+// which is again a tiled-pixel implicit GEMM whose output rows land in a phase view of dx.
+extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx, int NB, int H,
+                                        int W, int Cin, int Cout, int R, int stride,
+                                        void* stream) {
+  if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cout % 64) || (Cin % 8)) return -3;
+  if (stride == 2 && ((H | W) & 1)) return -3;
+  const int Ho = H / stride, Wo = W / stride;
+  const __nv_bfloat16* wtb = reinterpret_cast<const __nv_bfloat16*>(wt);
+  const int pad = R / 2;
+  long long wt_off = 0;
+  for (int py = 0; py < stride; ++py)
+    for (int px = 0; px < stride; ++px) {
+      GemmParams p{};
+      p.kind = 0;
+      p.BN = pick_bn(Cin);
+      pick_box(Wo, Ho, 128, &p.bw, &p.bh, &p.bn);
+      p.tiles_w = Wo / p.bw; p.tiles_h = Ho / p.bh;
+      p.tiles_m = p.tiles_w * p.tiles_h * ((NB + p.bn - 1) / p.bn);
+      p.tiles_n = (Cin + p.BN - 1) / p.BN;
+      p.splits = 1;
+      p.cin_blocks = Cout / 64;
+      int nt = 0;
+      for (int rr = 0; rr < R; ++rr)
+        for (int ss = 0; ss < R; ++ss) {
+          const int ey = py + pad - rr, ex = px + pad - ss;
+          if ((ey % stride) || (ex % stride)) continue;
+          p.taps[nt++] = Tap{0, (int8_t)(ex / stride), (int8_t)(ey / stride), 0};
+        }
+      p.ntaps = nt;
+      __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx) + ((long long)py * W + px) * Cin;
+      p.W = Wo; p.H = Ho; p.NB = NB;
+      p.C = dxp;
+      p.sW = (long long)stride * Cin; p.sH = (long long)stride * W * Cin;
+      p.sN = (long long)H * W * Cin;
+      p.n_valid = Cin; p.out_fp32 = 0; p.relu = 0; p.atomic = 0; p.bias = nullptr;
+      if (nt == 0) {
+        const long long total = (long long)NB * Ho * Wo * (Cin / 8);
+        int blocks = (int)((total + 255) / 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        zero_phase_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dxp, NB, Ho, Wo, Cin, p.sN, p.sH,
+                                                                    p.sW);
+        continue;
+      }
+      p.kb_total = nt * p.cin_blocks; p.kb_per_split = p.kb_total;
+      CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+      int box[4] = {64, p.bw, p.bh, p.bn};
+      long long dims[4] = {Cout, Wo, Ho, NB};
+      long long str[3] = {Cout, (long long)Wo * Cout, (long long)Ho * Wo * Cout};
+      int r = make_map4(&ma[0], dy, dims, str, box);
+      if (r) return r;
+      ma[1] = ma[2] = ma[3] = ma[0];
+      r = make_map2(&mb[0], wtb + wt_off, (long long)nt * Cout, Cin, (long long)nt * Cout, kBK, p.BN);
+      if (r) return r;
+      mb[1] = mb[2] = mb[3] = mb[0];
+      r = launch(ma, mb, p, (cudaStream_t)stream);
+      if (r) return r;
+      wt_off += (long long)nt * Cout * Cin;
+    }
+  return (int)cudaGetLastError();
+}
+
+// Filter re-layout for the data gradient (see b200dt_conv2d_dgrad_bf16). w: [Cout,R,R,Cin] bf16,
+// wt: R*R*Cout*Cin bf16.
+__global__ void filter_transpose_kernel(const __nv_bfloat16* __restrict__ w,
+                                        __nv_bfloat16* __restrict__ wt, int Cin, int Cout, int R,
+                                        int stride) {
+  const int pad = R / 2;
+  const long long total = (long long)R * R * Cout * Cin;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    // i enumerates the destination: phases, then [Cin][tap][Cout]
+    long long rem = i;
+    int found = 0;
+    for (int py = 0; py < stride && !found; ++py)
+      for (int px = 0; px < stride && !found; ++px) {
+        int taps_r[9], taps_s[9], nt = 0;
+        for (int rr = 0; rr < R; ++rr)
+          for (int ss = 0; ss < R; ++ss)
+            if (((py + pad - rr) % stride == 0) && ((px + pad - ss) % stride == 0)) {
+              taps_r[nt] = rr; taps_s[nt] = ss; ++nt;
+            }
+        const long long sz = (long long)nt * Cout * Cin;
+        if (rem < sz) {
+          const int co = (int)(rem % Cout);
+          const int t = (int)((rem / Cout) % nt);
+          const int ci = (int)(rem / ((long long)Cout * nt));
+          wt[i] = w[(((long long)co * R + taps_r[t]) * R + taps_s[t]) * Cin + ci];
+          found = 1;
+        } else {
+          rem -= sz;
+        }
+      }
+  }
+}
+
+extern "C" int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R,
+                                            int stride, void* stream) {
+  const long long total = (long long)R * R * Cout * Cin;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  filter_transpose_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(w), reinterpret_cast<__nv_bfloat16*>(wt), Cin, Cout, R,
+      stride);
+  return (int)cudaGetLastError();
+}

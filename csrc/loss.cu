@@ -1,0 +1,212 @@
+// Loss kernels: each call produces the scalar loss AND d(loss)/d(input) in one pass.
+// Replaces F.cross_entropy with probability targets (/root/reference/ddp_gpus.py:37), nn.MSELoss
+// (/root/reference/03.model_parallel.ipynb:533,976) and output.sum() (01.data_parallel.ipynb:485).
+//
+// The scalar is reduced in two levels without a second launch: every CTA writes its partial to
+// the scratch area, the last CTA to finish (ticket counter in the scratch area) adds the partials
+// in a fixed order, so the result is deterministic.  The counter is left at zero for the next call.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+constexpr int kLossMaxBlocks = 1024;
+struct LossScratch {
+  float partial[kLossMaxBlocks];
+  unsigned int ticket;
+  unsigned int pad[3];
+};
+
+// Called by all threads of the CTA with the CTA's partial in `v` (valid in thread 0).
+__device__ __forceinline__ void finish_scalar(float v, LossScratch* sc, float* out, float scale,
+                                              float* red) {
+  __shared__ bool is_last;
+  if (threadIdx.x == 0) {
+    sc->partial[blockIdx.x] = v;
+    __threadfence();
+    const unsigned int t = atomicAdd(&sc->ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    float s = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x)
+      s += *reinterpret_cast<volatile float*>(&sc->partial[i]);
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) {
+      *out = s * scale;
+      sc->ticket = 0;
+    }
+  }
+}
+
+template <typename T> __device__ __forceinline__ float ldf(const T* p, long long i);
+template <> __device__ __forceinline__ float ldf<float>(const float* p, long long i) { return p[i]; }
+template <> __device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p, long long i) {
+  return __bfloat162float(p[i]);
+}
+template <typename T> __device__ __forceinline__ void stf(T* p, long long i, float v);
+template <> __device__ __forceinline__ void stf<float>(float* p, long long i, float v) { p[i] = v; }
+template <> __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, long long i, float v) {
+  p[i] = __float2bfloat16(v);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+mse_kernel(const T* __restrict__ pred, const T* __restrict__ target, T* __restrict__ grad,
+           float* loss, long long n, float gscale, LossScratch* sc) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  const float gs = 2.f * gscale / (float)n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float d = ldf(pred, i) - ldf(target, i);
+    acc += d * d;
+    if (grad != nullptr) stf(grad, i, d * gs);
+  }
+  acc = block_sum(acc, red);
+  finish_scalar(acc, sc, loss, 1.f / (float)n, red);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+sum_kernel(const T* __restrict__ x, T* __restrict__ grad, float* loss, long long n, float gscale,
+           LossScratch* sc) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    acc += ldf(x, i);
+    if (grad != nullptr) stf(grad, i, gscale);
+  }
+  acc = block_sum(acc, red);
+  finish_scalar(acc, sc, loss, 1.f, red);
+}
+
+// One warp per row. kIndex: labels are class indices, else probability rows.
+template <typename T, bool kIndex>
+__global__ void __launch_bounds__(256)
+ce_kernel(const T* __restrict__ logits, const float* __restrict__ probs,
+          const long long* __restrict__ labels, T* __restrict__ grad, float* loss, int B, int C,
+          float gscale, LossScratch* sc) {
+  __shared__ float red[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  float acc = 0.f;
+  const float gs = gscale / (float)B;
+  for (int row = blockIdx.x * wpb + warp; row < B; row += gridDim.x * wpb) {
+    const T* x = logits + (long long)row * C;
+    float m = -INFINITY;
+    for (int c = lane; c < C; c += 32) m = fmaxf(m, ldf(x, c));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float se = 0.f, tsum = 0.f, tx = 0.f;
+    const long long lab = kIndex ? labels[row] : 0;
+    for (int c = lane; c < C; c += 32) {
+      const float v = ldf(x, c);
+      se += __expf(v - m);
+      if (kIndex) {
+        if (c == lab) { tsum = 1.f; tx = v; }
+      } else {
+        const float t = probs[(long long)row * C + c];
+        tsum += t;
+        tx += t * v;
+      }
+    }
+    se = warp_sum(se);
+    tsum = warp_sum(tsum);
+    tx = warp_sum(tx);
+    const float lse = m + __logf(se);
+    if (lane == 0) acc += lse * tsum - tx;
+    if (grad != nullptr) {
+      const float inv = 1.f / se;
+      for (int c = lane; c < C; c += 32) {
+        const float v = ldf(x, c);
+        const float sm = __expf(v - m) * inv;
+        float t;
+        if (kIndex) t = (c == lab) ? 1.f : 0.f;
+        else t = probs[(long long)row * C + c];
+        stf(grad + (long long)row * C, c, (sm * tsum - t) * gs);
+      }
+    }
+  }
+  acc = block_sum(acc, red);
+  finish_scalar(acc, sc, loss, 1.f / (float)B, red);
+}
+
+static int loss_grid(long long work_items) {
+  long long b = (work_items + 255) / 256;
+  if (b > 148 * 4) b = 148 * 4;
+  if (b > kLossMaxBlocks) b = kLossMaxBlocks;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" long long b200dt_loss_scratch_bytes(void) { return (long long)sizeof(LossScratch); }
+
+extern "C" int b200dt_mse_loss(const void* pred, const void* target, void* grad, float* loss,
+                               long long n, float grad_scale, int is_bf16, void* scratch,
+                               void* stream) {
+  if (n <= 0 || scratch == nullptr) return -3;
+  const int g = loss_grid(n);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    mse_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)pred,
+                                                 (const __nv_bfloat16*)target, (__nv_bfloat16*)grad,
+                                                 loss, n, grad_scale, (LossScratch*)scratch);
+  else
+    mse_kernel<float><<<g, 256, 0, st>>>((const float*)pred, (const float*)target, (float*)grad,
+                                         loss, n, grad_scale, (LossScratch*)scratch);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_sum_loss(const void* x, void* grad, float* loss, long long n,
+                               float grad_scale, int is_bf16, void* scratch, void* stream) {
+  if (n <= 0 || scratch == nullptr) return -3;
+  const int g = loss_grid(n);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    sum_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)grad,
+                                                 loss, n, grad_scale, (LossScratch*)scratch);
+  else
+    sum_kernel<float><<<g, 256, 0, st>>>((const float*)x, (float*)grad, loss, n, grad_scale,
+                                         (LossScratch*)scratch);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_ce_prob_loss(const void* logits, const float* probs, void* grad, float* loss,
+                                   int B, int C, float grad_scale, int is_bf16, void* scratch,
+                                   void* stream) {
+  if (B <= 0 || C <= 0 || scratch == nullptr) return -3;
+  const int g = loss_grid((long long)B * 32);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    ce_kernel<__nv_bfloat16, false><<<g, 256, 0, st>>>((const __nv_bfloat16*)logits, probs, nullptr,
+                                                       (__nv_bfloat16*)grad, loss, B, C, grad_scale,
+                                                       (LossScratch*)scratch);
+  else
+    ce_kernel<float, false><<<g, 256, 0, st>>>((const float*)logits, probs, nullptr, (float*)grad,
+                                               loss, B, C, grad_scale, (LossScratch*)scratch);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_ce_index_loss(const void* logits, const long long* labels, void* grad,
+                                    float* loss, int B, int C, float grad_scale, int is_bf16,
+                                    void* scratch, void* stream) {
+  if (B <= 0 || C <= 0 || scratch == nullptr) return -3;
+  const int g = loss_grid((long long)B * 32);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    ce_kernel<__nv_bfloat16, true><<<g, 256, 0, st>>>((const __nv_bfloat16*)logits, nullptr, labels,
+                                                      (__nv_bfloat16*)grad, loss, B, C, grad_scale,
+                                                      (LossScratch*)scratch);
+  else
+    ce_kernel<float, true><<<g, 256, 0, st>>>((const float*)logits, nullptr, labels, (float*)grad,
+                                              loss, B, C, grad_scale, (LossScratch*)scratch);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,182 @@
+// NHWC bf16 pooling: MaxPool 3x3 stride 2 pad 1 (with a 1-byte arg-max so the backward needs no
+// atomics) and global average pooling.  Replaces nn.MaxPool2d / nn.AdaptiveAvgPool2d of the
+// ResNet-50 in /root/reference/03.model_parallel.ipynb:815,824.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, uint2* __restrict__ argmax,
+                   int NB, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, cv = C / 8;
+  const long long total = (long long)NB * Ho * Wo * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv);
+    long long pix = i / cv;
+    const int wo = (int)(pix % Wo); pix /= Wo;
+    const int ho = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float best[8];
+    uint32_t arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = ho * 2 - 1 + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = wo * 2 - 1 + s;
+        if (w < 0 || w >= W) continue;
+        float f[8];
+        unpack8(ld_nc_v4(x + (((long long)n * H + h) * W + w) * cv + c), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; arg[j] = r * 3 + s; }
+      }
+    }
+    y[i] = pack8(best);
+    uint2 a;
+    a.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+    a.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    argmax[i] = a;
+  }
+}
+
+// One thread per input pixel x 8 channels: gather from the (at most four) windows covering it.
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const uint4* __restrict__ dy, const uint2* __restrict__ argmax,
+                   uint4* __restrict__ dx, int NB, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, cv = C / 8;
+  const long long total = (long long)NB * H * W * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv);
+    long long pix = i / cv;
+    const int w = (int)(pix % W); pix /= W;
+    const int h = (int)(pix % H);
+    const int n = (int)(pix / H);
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+    // windows ho with 2*ho - 1 <= h <= 2*ho + 1
+    for (int ho = (h) / 2; ho <= (h + 1) / 2; ++ho) {
+      if (ho < 0 || ho >= Ho) continue;
+      const int r = h - (ho * 2 - 1);
+      for (int wo = (w) / 2; wo <= (w + 1) / 2; ++wo) {
+        if (wo < 0 || wo >= Wo) continue;
+        const int s = w - (wo * 2 - 1);
+        const uint32_t code = r * 3 + s;
+        const long long o = (((long long)n * Ho + ho) * Wo + wo) * cv + c;
+        const uint2 a = argmax[o];
+        float d[8];
+        unpack8(ld_nc_v4(dy + o), d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t aj = ((j < 4 ? a.x : a.y) >> ((j & 3) * 8)) & 0xff;
+          if (aj == code) g[j] += d[j];
+        }
+      }
+    }
+    dx[i] = pack8(g);
+  }
+}
+
+// y[n, c] = mean over HW of x[n, hw, c]. One CTA per (n, 32-vector slab of channels).
+__global__ void __launch_bounds__(256)
+avgpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int HW, int C) {
+  __shared__ float red[8][32][9];
+  const int cv = C / 8;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;
+  const int n = blockIdx.y;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (col < cv)
+    for (int p = ty; p < HW; p += 8) {
+      float f[8];
+      unpack8(ld_nc_v4(x + ((long long)n * HW + p) * cv + col), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
+  __syncthreads();
+  if (ty == 0 && col < cv) {
+    for (int r = 1; r < 8; ++r)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += red[r][tx][j];
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    y[(long long)n * cv + col] = pack8(acc);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+avgpool_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int NB, int HW, int C) {
+  const int cv = C / 8;
+  const long long total = (long long)NB * HW * cv;
+  const float inv = 1.f / (float)HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv);
+    const int n = (int)(i / ((long long)HW * cv));
+    float f[8];
+    unpack8(dy[(long long)n * cv + c], f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= inv;
+    dx[i] = pack8(f);
+  }
+}
+
+static int grid_for(long long total) {
+  long long b = (total + 255) / 256;
+  if (b > 148 * 16) b = 148 * 16;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200dt_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int NB, int H, int W,
+                                       int C, void* stream) {
+  if ((C % 8) || ((H | W) & 1)) return -3;
+  const long long total = (long long)NB * (H / 2) * (W / 2) * (C / 8);
+  maxpool_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y),
+      reinterpret_cast<uint2*>(argmax), NB, H, W, C);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int NB,
+                                       int H, int W, int C, void* stream) {
+  if ((C % 8) || ((H | W) & 1)) return -3;
+  const long long total = (long long)NB * H * W * (C / 8);
+  maxpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint2*>(argmax),
+      reinterpret_cast<uint4*>(dx), NB, H, W, C);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_avgpool_fwd(const void* x, void* y, int NB, int HW, int C, void* stream) {
+  if (C % 8) return -3;
+  dim3 grid((C / 8 + 31) / 32, NB);
+  avgpool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(x),
+                                                             reinterpret_cast<uint4*>(y), HW, C);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_avgpool_bwd(const void* dy, void* dx, int NB, int HW, int C, void* stream) {
+  if (C % 8) return -3;
+  const long long total = (long long)NB * HW * (C / 8);
+  avgpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<uint4*>(dx), NB, HW, C);
+  return (int)cudaGetLastError();
+}

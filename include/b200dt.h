@@ -1,0 +1,171 @@
+/* b200dt — C ABI of the hand-written sm_100a kernels of this library.
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on (a cudaStream_t
+ * passed as void*), launches asynchronously, and returns 0 on success, a positive cudaError_t
+ * value for a CUDA failure, or a negative value for an argument the kernel cannot handle.
+ * Python binds these through ctypes (pytorch_distributed_training_tutorials_b200/_lib.py);
+ * the C++ gradient reducer calls them directly.
+ *
+ * "Replaces" cites the place in the reference tutorial (paths under /root/reference) where the
+ * equivalent library op (cuBLAS / cuDNN / ATen / NCCL) is reached.
+ */
+#ifndef B200DT_H_
+#define B200DT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- tcgen05 GEMM / implicit GEMM
+ * Replaces nn.Linear (ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)
+ * and the ResNet-50 convolutions (03.model_parallel.ipynb:807-833). csrc/gemm.cu */
+
+/* C[M,N] = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU); A, B bf16 row-major, C bf16 or fp32. */
+int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
+                        int ldb, int ldc, const float* bias, int relu, int out_fp32, void* stream);
+/* C[M,N] fp32 = A[Kr,M]^T * B[Kr,N] (weight gradients). splits = 0: library picks and clears C. */
+int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C, int M, int N, int Kr,
+                               int lda, int ldb, int ldc, int splits, void* stream);
+/* NHWC conv2d, square filter R in {1,3}, pad R/2, stride in {1,2}, Cin % 64 == 0. */
+int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, int NB, int H, int W, int Cin,
+                             int Cout, int R, int stride, int relu, void* stream);
+int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int NB, int H, int W,
+                             int Cin, int Cout, int R, int stride, void* stream);
+int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx, int NB, int H, int W,
+                             int Cin, int Cout, int R, int stride, void* stream);
+int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R, int stride,
+                                 void* stream);
+
+/* ---------------------------------------------------------------- layout / stem helpers
+ * Replaces the cuDNN 7x7 stem convolution's gather (03.model_parallel.ipynb:812). csrc/layout.cu */
+
+/* x: [NB,3,H,W] fp32 NCHW -> cols: [NB*Ho*Wo, ldk] bf16 with (r,s,c) ordering, 7x7 s2 p3. */
+int b200dt_stem_im2col(const float* x, void* cols, int NB, int H, int W, int ldk, void* stream);
+int b200dt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+int b200dt_transpose_bf16(const void* src, void* dst, int rows, int cols, void* stream);
+int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, int W, void* stream);
+
+/* ---------------------------------------------------------------- BatchNorm / ReLU / residual
+ * Replaces cuDNN BatchNorm + ATen relu/add in torchvision Bottleneck (03.model_parallel.ipynb:810).
+ * csrc/bn.cu.  x, y, residual, dy, dx, dres: [rows, C] bf16 (NHWC flattened); C % 8 == 0. */
+
+/* sums[0..C) = sum x, sums[C..2C) = sum x^2 (fp32, cleared by the call). */
+int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
+/* y = act(gamma * (x - mean) * invstd + beta (+ residual)); writes mean/invstd (fp32 [C] each)
+ * and updates running stats with `momentum` (unbiased variance), all from `sums`. */
+int b200dt_bn_apply(const void* x, const void* residual, void* y, const float* sums,
+                    const float* gamma, const float* beta, float* running_mean, float* running_var,
+                    float* save_mean, float* save_invstd, long long rows, int C, float eps,
+                    float momentum, int relu, void* stream);
+/* Inference-style apply with given statistics. */
+int b200dt_bn_apply_eval(const void* x, const void* residual, void* y, const float* gamma,
+                         const float* beta, const float* mean, const float* var, long long rows,
+                         int C, float eps, int relu, void* stream);
+/* Backward phase 1: g = dy * (y > 0 if relu); sums[0..C) = sum g, sums[C..2C) = sum g * xhat;
+ * optionally writes g to dres (gradient of the residual branch). */
+int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x, const float* save_mean,
+                         const float* save_invstd, float* sums, void* dres, long long rows, int C,
+                         int relu, void* stream);
+/* Backward phase 2: dx = gamma*invstd*(g - sum_g/rows - xhat*sum_gx/rows); dgamma, dbeta fp32. */
+int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x, const float* save_mean,
+                        const float* save_invstd, const float* gamma, const float* sums, void* dx,
+                        float* dgamma, float* dbeta, long long rows, int C, int relu, void* stream);
+
+/* ---------------------------------------------------------------- pooling (csrc/pool.cu)
+ * Replaces nn.MaxPool2d(3,2,1) / AdaptiveAvgPool2d(1) (03.model_parallel.ipynb:815,824). */
+int b200dt_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int NB, int H, int W, int C,
+                            void* stream);
+int b200dt_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int NB, int H, int W,
+                            int C, void* stream);
+int b200dt_avgpool_fwd(const void* x, void* y, int NB, int HW, int C, void* stream);
+int b200dt_avgpool_bwd(const void* dy, void* dx, int NB, int HW, int C, void* stream);
+
+/* ---------------------------------------------------------------- losses (csrc/loss.cu)
+ * Replaces F.cross_entropy (ddp_gpus.py:37), nn.MSELoss (03.model_parallel.ipynb:533,976) and
+ * output.sum() (01.data_parallel.ipynb:485). Each call computes loss and d(loss)/d(pred). */
+
+/* Scratch for the two-pass reductions below: at least b200dt_loss_scratch_bytes() bytes. */
+long long b200dt_loss_scratch_bytes(void);
+/* loss = mean((pred - target)^2); grad = 2*(pred - target)/n * grad_scale. pred/target fp32 or
+ * bf16 (is_bf16), grad has the dtype of pred, loss fp32[1]. grad may be NULL. */
+int b200dt_mse_loss(const void* pred, const void* target, void* grad, float* loss, long long n,
+                    float grad_scale, int is_bf16, void* scratch, void* stream);
+/* loss = sum(x); grad = grad_scale everywhere (may be NULL). */
+int b200dt_sum_loss(const void* x, void* grad, float* loss, long long n, float grad_scale,
+                    int is_bf16, void* scratch, void* stream);
+/* Soft-target cross entropy, mean over rows: logits [B,C], probs [B,C] fp32 targets. */
+int b200dt_ce_prob_loss(const void* logits, const float* probs, void* grad, float* loss, int B,
+                        int C, float grad_scale, int is_bf16, void* scratch, void* stream);
+/* Class-index cross entropy, mean over rows: labels int64[B]. */
+int b200dt_ce_index_loss(const void* logits, const long long* labels, void* grad, float* loss,
+                         int B, int C, float grad_scale, int is_bf16, void* scratch, void* stream);
+
+/* ---------------------------------------------------------------- optimizers (csrc/optim.cu)
+ * Replaces torch.optim.SGD (ddp_gpus.py:82) / Adam (01.data_parallel.ipynb:287) foreach kernels.
+ * meta: device int64 [n_tensors, 8] = {param, grad, shadow_bf16|0, numel, exp_avg|0, exp_avg_sq|0,
+ * 0, 0}; chunks: device int32 [n_chunks, 2] = {tensor index, first element}; every chunk covers
+ * at most B200DT_OPT_CHUNK elements. */
+#define B200DT_OPT_CHUNK 8192
+int b200dt_multi_sgd(const long long* meta, const int* chunks, int n_chunks, float lr,
+                     float weight_decay, float grad_scale, int zero_grad, void* stream);
+int b200dt_multi_adam(const long long* meta, const int* chunks, int n_chunks, float lr, float beta1,
+                      float beta2, float eps, float weight_decay, int step, float grad_scale,
+                      int zero_grad, void* stream);
+
+/* ---------------------------------------------------------------- multi-process collectives
+ * Replaces the NCCL all-reduce / broadcast issued by DistributedDataParallel (ddp_gpus.py:32,38)
+ * together with the Reducer's copy-in / copy-out. csrc/allreduce.cu.
+ *
+ * One launch = gather the listed tensors (scaled, cast to the wire dtype) into this rank's
+ * symmetric staging buffer -> cross-GPU barrier -> reduce over peer memory (mode 0 one-shot,
+ * 1 two-shot, 2 NVLS multimem) or broadcast from `root` (mode 3) -> scatter the result back into
+ * the tensors. `bufs` / `sigs` are HOST arrays of `world` peer-mapped device addresses: every
+ * rank's symmetric buffer and its signal pad (uint32 words, zero-initialised, at least
+ * B200DT_SIGNAL_WORDS of them). `mc` is the multicast address of the symmetric buffer (0 if none;
+ * required for mode 2). `tensors`: device array of {void* ptr; int64 numel}. `chunks`: device array
+ * of {int32 tensor, int32 start, int32 len, int32 pad, int64 stage_off}; stage_off is in elements,
+ * a multiple of 8. All ranks must pass identical chunk tables, `grid` and `sig_base`. `status`
+ * (device int32) becomes non-zero if a peer did not arrive within the spin bound. */
+#define B200DT_SIGNAL_WORDS 8192
+#define B200DT_MAX_WORLD 8
+int b200dt_coll_chunk_bytes(void);
+int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t* sigs, uint64_t mc, int rank,
+                       int world, int root, const void* tensors, const void* chunks, int n_chunks,
+                       long long stage_base_bytes, int tensor_bf16, int wire_bf16, float scale,
+                       int sig_base, int grid, int* status, void* stream);
+/* fp32 gradient -> (scaled) bucket slot, optionally as bf16 (NCCL / gloo fallback copy-in). */
+int b200dt_scale_cast(const float* src, void* dst, long long n, float scale, int dst_bf16,
+                      void* stream);
+/* bucket slot (fp32 or bf16) -> fp32 gradient (fallback copy-out). */
+int b200dt_cast_to_f32(const void* src, float* dst, long long n, int src_bf16, void* stream);
+/* Single-GPU emulation of the reduce arithmetic of `world` ranks: out = sum_r scale * bufs[r];
+ * dtype 0 fp32, 1 bf16 (for tests on one GPU). bufs: HOST array of device addresses. */
+int b200dt_allreduce_local_emulate(const uint64_t* bufs, int world, void* out, long long n,
+                                   int dtype, float scale, void* stream);
+
+/* ---------------------------------------------------------------- single-process peer kernels
+ * Replaces torch._C._broadcast_coalesced / _scatter / _gather / nccl.reduce behind nn.DataParallel
+ * (01.data_parallel.ipynb:275,482,486). csrc/p2p.cu. Pointers are peer-mapped device pointers of
+ * ONE process; ordering between devices is by CUDA events, not in-kernel flags. */
+int b200dt_enable_peer_access(int dev, int peer);
+/* src on the current device is stored to up to 8 destinations (peer pointers) in one pass. */
+int b200dt_p2p_broadcast(const void* src, const uint64_t* dsts_host, int ndst, long long nbytes,
+                         void* stream);
+/* dst (current device) = sum of nsrc peer buffers (fp32), scaled. */
+int b200dt_p2p_reduce_f32(float* dst, const uint64_t* srcs_host, int nsrc, long long n,
+                          float scale, int accumulate, void* stream);
+/* Copy rows [row0, row0+rows) x row_bytes from the current device into dst (peer) and, if
+ * partial != NULL, also add sum(src) (fp32 data) into *partial: gather fused with the loss sum. */
+int b200dt_p2p_gather_rows(const void* src, void* dst_peer, long long nbytes, float* partial_peer,
+                           int is_f32, void* stream);
+
+/* ---------------------------------------------------------------- misc */
+int b200dt_device_sm_count(void);
+const char* b200dt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DT_H_ */

@@ -1,0 +1,131 @@
+"""ctypes binding of ``_native/libb200dt.so`` (the C ABI declared in ``include/b200dt.h``).
+
+The library is loaded lazily on first use.  On a machine with a GPU a missing or unloadable
+library is a hard error: there is no eager / PyTorch fallback for the CUDA ops of this package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Optional
+
+import torch
+
+_lock = threading.Lock()
+_lib: Optional[C.CDLL] = None
+
+vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint64
+
+_SIGS = {
+    "b200dt_gemm_tn_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp],
+    "b200dt_gemm_nt_reduce_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
+    "b200dt_conv2d_fprop_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "b200dt_conv2d_wgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
+    "b200dt_conv2d_dgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
+    "b200dt_filter_transpose_bf16": [vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_stem_im2col": [vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_cast_f32_to_bf16": [vp, vp, i64, vp],
+    "b200dt_transpose_bf16": [vp, vp, i32, i32, vp],
+    "b200dt_nchw_f32_to_nhwc_bf16": [vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_bn_stats": [vp, vp, i64, i32, vp],
+    "b200dt_bn_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp],
+    "b200dt_bn_apply_eval": [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp],
+    "b200dt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
+    "b200dt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
+    "b200dt_maxpool3x3s2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_maxpool3x3s2_bwd": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_avgpool_fwd": [vp, vp, i32, i32, i32, vp],
+    "b200dt_avgpool_bwd": [vp, vp, i32, i32, i32, vp],
+    "b200dt_mse_loss": [vp, vp, vp, vp, i64, f32, i32, vp, vp],
+    "b200dt_sum_loss": [vp, vp, vp, i64, f32, i32, vp, vp],
+    "b200dt_ce_prob_loss": [vp, vp, vp, vp, i32, i32, f32, i32, vp, vp],
+    "b200dt_ce_index_loss": [vp, vp, vp, vp, i32, i32, f32, i32, vp, vp],
+    "b200dt_multi_sgd": [vp, vp, i32, f32, f32, f32, i32, vp],
+    "b200dt_multi_adam": [vp, vp, i32, f32, f32, f32, f32, f32, i32, f32, i32, vp],
+    "b200dt_coll_launch": [i32, vp, vp, u64, i32, i32, i32, vp, vp, i32, i64, i32, i32, f32, i32,
+                           i32, vp, vp],
+    "b200dt_scale_cast": [vp, vp, i64, f32, i32, vp],
+    "b200dt_cast_to_f32": [vp, vp, i64, i32, vp],
+    "b200dt_allreduce_local_emulate": [vp, i32, vp, i64, i32, f32, vp],
+    "b200dt_enable_peer_access": [i32, i32],
+    "b200dt_p2p_broadcast": [vp, vp, i32, i64, vp],
+    "b200dt_p2p_reduce_f32": [vp, vp, i32, i64, f32, i32, vp],
+    "b200dt_p2p_gather_rows": [vp, vp, i64, vp, i32, vp],
+}
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+def available() -> bool:
+    """True if the compiled kernel library exists on disk (it is only usable with a GPU)."""
+    from .build import lib_path
+
+    return lib_path().exists()
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        from .build import lib_path
+
+        path = lib_path()
+        if not path.exists():
+            raise NativeLibraryError(
+                f"{path} is missing: run `python -m pytorch_distributed_training_tutorials_b200.build` "
+                "(nvcc, sm_100a). The CUDA ops of this package have no PyTorch fallback."
+            )
+        try:
+            handle = C.CDLL(str(path), mode=C.RTLD_GLOBAL)
+        except OSError as e:  # pragma: no cover - depends on the box
+            raise NativeLibraryError(f"cannot load {path}: {e}") from e
+        for name, argtypes in _SIGS.items():
+            fn = getattr(handle, name)
+            fn.argtypes = argtypes
+            fn.restype = i32
+        handle.b200dt_loss_scratch_bytes.restype = i64
+        handle.b200dt_loss_scratch_bytes.argtypes = []
+        handle.b200dt_coll_chunk_bytes.restype = i32
+        handle.b200dt_coll_chunk_bytes.argtypes = []
+        handle.b200dt_device_sm_count.restype = i32
+        handle.b200dt_version.restype = C.c_char_p
+        _lib = handle
+        return handle
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc == 0:
+        return
+    if rc > 0:
+        try:
+            msg = torch.cuda.cudart().cudaGetErrorString(rc)
+        except Exception:  # pragma: no cover
+            msg = "cuda error"
+        raise RuntimeError(f"b200dt {what}: CUDA error {rc}: {msg}")
+    reasons = {
+        -1: "cuTensorMapEncodeTiled entry point not found",
+        -2: "tile configuration does not fit in shared memory",
+        -3: "unsupported shape / alignment / dtype for this kernel",
+        -4: "NVLS requested but no multicast address",
+        -5: "not enough signal-pad words for this grid",
+        -6: "peer access not possible between these devices",
+    }
+    raise RuntimeError(f"b200dt {what}: error {rc}: {reasons.get(rc, 'tensor map encode failed' if rc < -1000 else 'invalid argument')}")
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def u64_array(values) -> C.Array:
+    arr = (u64 * len(values))(*[int(v) for v in values])
+    return arr

@@ -1,0 +1,300 @@
+"""Tensor-level wrappers over the C ABI (one Python function per kernel entry point).
+
+These do shape / dtype checks, allocate outputs with torch's caching allocator and launch on the
+current CUDA stream.  No autograd here; see ``functional.py`` for the differentiable ops.
+All activations are NHWC bf16 (``[N, H, W, C]`` contiguous), weights ``[Cout, R, S, Cin]`` bf16.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from .. import _lib
+from .._lib import check, lib, ptr, stream_ptr
+
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _need(t: torch.Tensor, dtype, name: str) -> None:
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name}: expected a contiguous CUDA {dtype} tensor, got {t.dtype} on {t.device} "
+                         f"(contiguous={t.is_contiguous()})")
+
+
+# --------------------------------------------------------------------------- GEMM / conv
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+            out_dtype=BF16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``a[M,K] @ b[N,K]^T (+bias) (relu)``; bf16 inputs, fp32 accumulation on tcgen05."""
+    _need(a, BF16, "a"); _need(b, BF16, "b")
+    M, K = a.shape
+    N, K2 = b.shape
+    if K != K2 or K % 8:
+        raise ValueError(f"gemm_tn: K mismatch or K % 8 != 0 ({K}, {K2})")
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    if bias is not None:
+        _need(bias, F32, "bias")
+    with torch.cuda.device(a.device):
+        check(lib().b200dt_gemm_tn_bf16(ptr(a), ptr(b), ptr(out), M, N, K, K, K, out.stride(0),
+                                        ptr(bias), int(relu), int(out.dtype == F32),
+                                        stream_ptr(a.device)), "gemm_tn")
+    return out
+
+
+def gemm_nt_reduce(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``a[R,M]^T @ b[R,N]`` -> fp32 ``[M,N]`` (weight gradients; reduction over rows)."""
+    _need(a, BF16, "a"); _need(b, BF16, "b")
+    R, M = a.shape
+    R2, N = b.shape
+    if R != R2 or M % 8 or N % 8:
+        raise ValueError("gemm_nt_reduce: row mismatch or M/N % 8 != 0")
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=F32)
+    with torch.cuda.device(a.device):
+        check(lib().b200dt_gemm_nt_reduce_bf16(ptr(a), ptr(b), ptr(out), M, N, R, M, N, out.stride(0), 0,
+                                               stream_ptr(a.device)), "gemm_nt_reduce")
+    return out
+
+
+def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool = False) -> torch.Tensor:
+    _need(x, BF16, "x"); _need(w, BF16, "w")
+    NB, H, W, Cin = x.shape
+    Cout, R, S, Cin2 = w.shape
+    assert R == S and Cin == Cin2
+    y = torch.empty((NB, H // stride, W // stride, Cout), device=x.device, dtype=BF16)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_conv2d_fprop_bf16(ptr(x), ptr(w), ptr(y), NB, H, W, Cin, Cout, R, stride,
+                                             int(relu), stream_ptr(x.device)), "conv2d_fprop")
+    return y
+
+
+def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, R: int, stride: int = 1,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _need(x, BF16, "x"); _need(dy, BF16, "dy")
+    NB, H, W, Cin = x.shape
+    Cout = dy.shape[-1]
+    if out is None:
+        out = torch.empty((Cout, R, R, Cin), device=x.device, dtype=F32)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_conv2d_wgrad_bf16(ptr(x), ptr(dy), ptr(out), NB, H, W, Cin, Cout, R, stride,
+                                             stream_ptr(x.device)), "conv2d_wgrad")
+    return out
+
+
+def filter_transpose(w: torch.Tensor, stride: int = 1) -> torch.Tensor:
+    _need(w, BF16, "w")
+    Cout, R, S, Cin = w.shape
+    wt = torch.empty(R * S * Cout * Cin, device=w.device, dtype=BF16)
+    with torch.cuda.device(w.device):
+        check(lib().b200dt_filter_transpose_bf16(ptr(w), ptr(wt), Cin, Cout, R, stride,
+                                                 stream_ptr(w.device)), "filter_transpose")
+    return wt
+
+
+def conv2d_dgrad(dy: torch.Tensor, wt: torch.Tensor, x_shape, R: int, stride: int = 1) -> torch.Tensor:
+    _need(dy, BF16, "dy"); _need(wt, BF16, "wt")
+    NB, H, W, Cin = x_shape
+    Cout = dy.shape[-1]
+    dx = torch.empty((NB, H, W, Cin), device=dy.device, dtype=BF16)
+    with torch.cuda.device(dy.device):
+        check(lib().b200dt_conv2d_dgrad_bf16(ptr(dy), ptr(wt), ptr(dx), NB, H, W, Cin, Cout, R, stride,
+                                             stream_ptr(dy.device)), "conv2d_dgrad")
+    return dx
+
+
+# --------------------------------------------------------------------------- layout
+STEM_LDK = 160
+
+
+def stem_im2col(x: torch.Tensor) -> torch.Tensor:
+    """[N,3,H,W] fp32 NCHW -> [N*H/2*W/2, 160] bf16 patches of the 7x7 stride-2 stem."""
+    _need(x, F32, "x")
+    NB, C, H, W = x.shape
+    assert C == 3
+    cols = torch.empty((NB * (H // 2) * (W // 2), STEM_LDK), device=x.device, dtype=BF16)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_stem_im2col(ptr(x), ptr(cols), NB, H, W, STEM_LDK, stream_ptr(x.device)),
+              "stem_im2col")
+    return cols
+
+
+def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _need(src, F32, "src")
+    if out is None:
+        out = torch.empty(src.shape, device=src.device, dtype=BF16)
+    with torch.cuda.device(src.device):
+        check(lib().b200dt_cast_f32_to_bf16(ptr(src), ptr(out), src.numel(), stream_ptr(src.device)), "cast")
+    return out
+
+
+def transpose_bf16(src: torch.Tensor) -> torch.Tensor:
+    _need(src, BF16, "src")
+    r, c = src.shape
+    out = torch.empty((c, r), device=src.device, dtype=BF16)
+    with torch.cuda.device(src.device):
+        check(lib().b200dt_transpose_bf16(ptr(src), ptr(out), r, c, stream_ptr(src.device)), "transpose")
+    return out
+
+
+def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    _need(x, F32, "x")
+    NB, Cc, H, W = x.shape
+    y = torch.empty((NB, H, W, Cc), device=x.device, dtype=BF16)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_nchw_f32_to_nhwc_bf16(ptr(x), ptr(y), NB, Cc, H, W, stream_ptr(x.device)), "nchw_to_nhwc")
+    return y
+
+
+# --------------------------------------------------------------------------- batch norm
+def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
+    rows, Cc = x2d.shape
+    sums = torch.empty(2 * Cc, device=x2d.device, dtype=F32)
+    with torch.cuda.device(x2d.device):
+        check(lib().b200dt_bn_stats(ptr(x2d), ptr(sums), rows, Cc, stream_ptr(x2d.device)), "bn_stats")
+    return sums
+
+
+def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, momentum, relu
+             ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    rows, Cc = x2d.shape
+    y = torch.empty_like(x2d)
+    save_mean = torch.empty(Cc, device=x2d.device, dtype=F32)
+    save_invstd = torch.empty(Cc, device=x2d.device, dtype=F32)
+    with torch.cuda.device(x2d.device):
+        check(lib().b200dt_bn_apply(ptr(x2d), ptr(residual), ptr(y), ptr(sums), ptr(gamma), ptr(beta),
+                                    ptr(running_mean), ptr(running_var), ptr(save_mean), ptr(save_invstd),
+                                    rows, Cc, eps, momentum, int(relu), stream_ptr(x2d.device)), "bn_apply")
+    return y, save_mean, save_invstd
+
+
+def bn_apply_eval(x2d, residual, gamma, beta, mean, var, eps, relu) -> torch.Tensor:
+    rows, Cc = x2d.shape
+    y = torch.empty_like(x2d)
+    with torch.cuda.device(x2d.device):
+        check(lib().b200dt_bn_apply_eval(ptr(x2d), ptr(residual), ptr(y), ptr(gamma), ptr(beta), ptr(mean),
+                                         ptr(var), rows, Cc, eps, int(relu), stream_ptr(x2d.device)), "bn_eval")
+    return y
+
+
+def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_dres: bool):
+    """Returns (dx, dgamma, dbeta, dres or None)."""
+    rows, Cc = x2d.shape
+    dev = x2d.device
+    sums = torch.empty(2 * Cc, device=dev, dtype=F32)
+    dres = torch.empty_like(dy2d) if want_dres else None
+    dx = torch.empty_like(x2d)
+    dgamma = torch.empty(Cc, device=dev, dtype=F32)
+    dbeta = torch.empty(Cc, device=dev, dtype=F32)
+    with torch.cuda.device(dev):
+        st = stream_ptr(dev)
+        check(lib().b200dt_bn_bwd_reduce(ptr(dy2d), ptr(y2d), ptr(x2d), ptr(save_mean), ptr(save_invstd),
+                                         ptr(sums), ptr(dres), rows, Cc, int(relu), st), "bn_bwd_reduce")
+        if want_dres:   # masked gradient already materialised: reuse it, skip the y read
+            check(lib().b200dt_bn_bwd_apply(ptr(dres), None, ptr(x2d), ptr(save_mean), ptr(save_invstd),
+                                            ptr(gamma), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta), rows, Cc,
+                                            0, st), "bn_bwd_apply")
+        else:
+            check(lib().b200dt_bn_bwd_apply(ptr(dy2d), ptr(y2d), ptr(x2d), ptr(save_mean), ptr(save_invstd),
+                                            ptr(gamma), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta), rows, Cc,
+                                            int(relu), st), "bn_bwd_apply")
+    return dx, dgamma, dbeta, dres
+
+
+# --------------------------------------------------------------------------- pooling
+def maxpool_fwd(x: torch.Tensor):
+    NB, H, W, Cc = x.shape
+    y = torch.empty((NB, H // 2, W // 2, Cc), device=x.device, dtype=BF16)
+    arg = torch.empty((NB, H // 2, W // 2, Cc), device=x.device, dtype=torch.uint8)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_maxpool3x3s2_fwd(ptr(x), ptr(y), ptr(arg), NB, H, W, Cc, stream_ptr(x.device)), "maxpool")
+    return y, arg
+
+
+def maxpool_bwd(dy: torch.Tensor, arg: torch.Tensor, x_shape) -> torch.Tensor:
+    NB, H, W, Cc = x_shape
+    dx = torch.empty(x_shape, device=dy.device, dtype=BF16)
+    with torch.cuda.device(dy.device):
+        check(lib().b200dt_maxpool3x3s2_bwd(ptr(dy), ptr(arg), ptr(dx), NB, H, W, Cc, stream_ptr(dy.device)), "maxpool_bwd")
+    return dx
+
+
+def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
+    NB, H, W, Cc = x.shape
+    y = torch.empty((NB, Cc), device=x.device, dtype=BF16)
+    with torch.cuda.device(x.device):
+        check(lib().b200dt_avgpool_fwd(ptr(x), ptr(y), NB, H * W, Cc, stream_ptr(x.device)), "avgpool")
+    return y
+
+
+def avgpool_bwd(dy: torch.Tensor, x_shape) -> torch.Tensor:
+    NB, H, W, Cc = x_shape
+    dx = torch.empty(x_shape, device=dy.device, dtype=BF16)
+    with torch.cuda.device(dy.device):
+        check(lib().b200dt_avgpool_bwd(ptr(dy), ptr(dx), NB, H * W, Cc, stream_ptr(dy.device)), "avgpool_bwd")
+    return dx
+
+
+# --------------------------------------------------------------------------- losses
+_scratch = {}
+
+
+def loss_scratch(device) -> torch.Tensor:
+    """Per-(device, stream) zero-initialised scratch for the two-level loss reductions."""
+    key = (torch.device(device).index, torch.cuda.current_stream(device).cuda_stream)
+    s = _scratch.get(key)
+    if s is None:
+        n = int(lib().b200dt_loss_scratch_bytes())
+        s = torch.zeros(n, device=device, dtype=torch.uint8)
+        _scratch[key] = s
+    return s
+
+
+def _loss_common(kind: str, pred: torch.Tensor, other, grad_scale: float, want_grad: bool):
+    dev = pred.device
+    is_bf16 = pred.dtype == BF16
+    if pred.dtype not in (BF16, F32) or not pred.is_contiguous():
+        raise ValueError("loss input must be contiguous fp32 or bf16")
+    loss = torch.empty((), device=dev, dtype=F32)
+    grad = torch.empty_like(pred) if want_grad else None
+    with torch.cuda.device(dev):
+        sc = loss_scratch(dev)
+        st = stream_ptr(dev)
+        L = lib()
+        if kind == "mse":
+            other = other.to(dtype=pred.dtype).contiguous()
+            check(L.b200dt_mse_loss(ptr(pred), ptr(other), ptr(grad), ptr(loss), pred.numel(), grad_scale,
+                                    int(is_bf16), ptr(sc), st), "mse")
+        elif kind == "sum":
+            check(L.b200dt_sum_loss(ptr(pred), ptr(grad), ptr(loss), pred.numel(), grad_scale, int(is_bf16),
+                                    ptr(sc), st), "sum")
+        elif kind == "ce_prob":
+            B, Cc = pred.shape
+            other = other.to(dtype=F32).contiguous()
+            check(L.b200dt_ce_prob_loss(ptr(pred), ptr(other), ptr(grad), ptr(loss), B, Cc, grad_scale,
+                                        int(is_bf16), ptr(sc), st), "ce_prob")
+        elif kind == "ce_index":
+            B, Cc = pred.shape
+            other = other.to(dtype=torch.int64).contiguous()
+            check(L.b200dt_ce_index_loss(ptr(pred), ptr(other), ptr(grad), ptr(loss), B, Cc, grad_scale,
+                                         int(is_bf16), ptr(sc), st), "ce_index")
+        else:  # pragma: no cover
+            raise ValueError(kind)
+    return loss, grad
+
+
+def mse_loss_fwd_bwd(pred, target, grad_scale=1.0, want_grad=True):
+    return _loss_common("mse", pred, target, grad_scale, want_grad)
+
+
+def sum_loss_fwd_bwd(x, grad_scale=1.0, want_grad=True):
+    return _loss_common("sum", x, None, grad_scale, want_grad)
+
+
+def ce_prob_fwd_bwd(logits, probs, grad_scale=1.0, want_grad=True):
+    return _loss_common("ce_prob", logits, probs, grad_scale, want_grad)
+
+
+def ce_index_fwd_bwd(logits, labels, grad_scale=1.0, want_grad=True):
+    return _loss_common("ce_index", logits, labels, grad_scale, want_grad)

@@ -1,0 +1,211 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from pytorch_distributed_training_tutorials_b200.ops import native as NV
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def rel_err(a, b):
+    a = a.float(); b = b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def nhwc(x_nchw):
+    return x_nchw.permute(0, 2, 3, 1).contiguous()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 128, 128), (1000, 1000, 2048), (4096, 256, 512),
+                                   (300, 72, 200), (32, 8, 24), (8192, 2048, 1024), (20000, 512, 64)])
+def test_gemm_tn(M, N, K):
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=dev()).bfloat16()
+    b = torch.randn(N, K, device=dev()).bfloat16()
+    bias = torch.randn(N, device=dev())
+    ref = a.float() @ b.float().t()
+    out = NV.gemm_tn(a, b)
+    assert rel_err(out, ref) < 1e-2
+    out2 = NV.gemm_tn(a, b, bias=bias, relu=True, out_dtype=torch.float32)
+    assert rel_err(out2, torch.relu(ref + bias)) < 2e-3
+
+
+@pytest.mark.parametrize("R,M,N", [(64, 64, 64), (4096, 128, 128), (1000, 1000, 2048), (777, 72, 200),
+                                   (100000, 64, 64), (32768, 256, 64)])
+def test_gemm_nt_reduce(R, M, N):
+    torch.manual_seed(0)
+    a = torch.randn(R, M, device=dev()).bfloat16()
+    b = torch.randn(R, N, device=dev()).bfloat16()
+    ref = a.float().t() @ b.float()
+    out = NV.gemm_nt_reduce(a, b)
+    assert rel_err(out, ref) < 2e-3
+
+
+CONVS = [  # (NB, H, W, Cin, Cout, R, stride)
+    (8, 56, 56, 64, 64, 1, 1), (8, 56, 56, 64, 64, 3, 1), (8, 56, 56, 64, 256, 1, 1),
+    (8, 56, 56, 256, 128, 1, 1), (8, 56, 56, 128, 128, 3, 2), (8, 56, 56, 256, 512, 1, 2),
+    (32, 28, 28, 128, 128, 3, 1), (32, 28, 28, 256, 256, 3, 2), (32, 14, 14, 256, 256, 3, 1),
+    (32, 14, 14, 512, 512, 3, 2), (128, 7, 7, 512, 512, 3, 1), (128, 7, 7, 512, 2048, 1, 1),
+    (5, 28, 28, 128, 128, 3, 1), (3, 14, 14, 1024, 256, 1, 1), (130, 7, 7, 2048, 512, 1, 1),
+]
+
+
+def conv_ref(x, w, stride):
+    # x: NHWC bf16, w: [Cout,R,S,Cin] bf16 -> fp32 NCHW reference
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wr = w.float().permute(0, 3, 1, 2).requires_grad_(True)
+    y = F.conv2d(xr, wr, stride=stride, padding=w.shape[1] // 2)
+    return xr, wr, y
+
+
+@pytest.mark.parametrize("cfg", CONVS)
+def test_conv_fprop(cfg):
+    NB, H, W, Cin, Cout, R, s = cfg
+    torch.manual_seed(1)
+    x = torch.randn(NB, H, W, Cin, device=dev()).bfloat16()
+    w = (torch.randn(Cout, R, R, Cin, device=dev()) / (R * Cin ** 0.5)).bfloat16()
+    _, _, yref = conv_ref(x, w, s)
+    y = NV.conv2d_fprop(x, w, stride=s)
+    assert y.shape == (NB, H // s, W // s, Cout)
+    assert rel_err(y, nhwc(yref)) < 1e-2
+
+
+@pytest.mark.parametrize("cfg", CONVS)
+def test_conv_dgrad_wgrad(cfg):
+    NB, H, W, Cin, Cout, R, s = cfg
+    torch.manual_seed(2)
+    x = torch.randn(NB, H, W, Cin, device=dev()).bfloat16()
+    w = (torch.randn(Cout, R, R, Cin, device=dev()) / (R * Cin ** 0.5)).bfloat16()
+    dy = torch.randn(NB, H // s, W // s, Cout, device=dev()).bfloat16()
+    xr, wr, yref = conv_ref(x, w, s)
+    yref.backward(dy.float().permute(0, 3, 1, 2))
+    dw = NV.conv2d_wgrad(x, dy, R, stride=s)
+    assert rel_err(dw, wr.grad.permute(0, 2, 3, 1)) < 5e-3
+    wt = NV.filter_transpose(w, stride=s)
+    dx = NV.conv2d_dgrad(dy, wt, x.shape, R, stride=s)
+    assert rel_err(dx, nhwc(xr.grad)) < 1e-2
+
+
+def test_stem_im2col_conv():
+    torch.manual_seed(3)
+    x = torch.randn(4, 3, 64, 64, device=dev())
+    w = torch.randn(64, 3, 7, 7, device=dev()) * 0.05
+    cols = NV.stem_im2col(x)
+    wk = torch.zeros(64, NV.STEM_LDK, device=dev())
+    wk[:, :147] = w.permute(0, 2, 3, 1).reshape(64, 147)
+    y = NV.gemm_tn(cols, wk.bfloat16())
+    ref = F.conv2d(x.bfloat16().float(), w.bfloat16().float(), stride=2, padding=3)
+    assert rel_err(y.view(4, 32, 32, 64), nhwc(ref)) < 1e-2
+
+
+@pytest.mark.parametrize("rows,C", [(8 * 56 * 56, 64), (4 * 28 * 28, 512), (1000, 2048), (37, 24)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
+def test_batchnorm(rows, C, relu, res):
+    torch.manual_seed(4)
+    x = (torch.randn(rows, C, device=dev()) * 2 + 0.5).bfloat16()
+    r = torch.randn(rows, C, device=dev()).bfloat16() if res else None
+    g = torch.rand(C, device=dev()) + 0.5
+    b = torch.randn(C, device=dev())
+    rm = torch.zeros(C, device=dev()); rv = torch.ones(C, device=dev())
+    xr = x.float().requires_grad_(True)
+    rr = r.float().requires_grad_(True) if res else None
+    rm_ref = rm.clone(); rv_ref = rv.clone()
+    yref = F.batch_norm(xr, rm_ref, rv_ref, g, b, True, 0.1, 1e-5)
+    if res:
+        yref = yref + rr
+    if relu:
+        yref = torch.relu(yref)
+    sums = NV.bn_stats(x)
+    y, mean, invstd = NV.bn_apply(x, r, sums, g, b, rm, rv, 1e-5, 0.1, relu)
+    assert rel_err(y, yref) < 1e-2
+    assert torch.allclose(rm, rm_ref, atol=1e-3, rtol=1e-3)
+    assert torch.allclose(rv, rv_ref, atol=1e-3, rtol=1e-3)
+    dy = torch.randn(rows, C, device=dev()).bfloat16()
+    gref = g.clone().requires_grad_(True)
+    bref = b.clone().requires_grad_(True)
+    y2 = F.batch_norm(xr, None, None, gref, bref, True, 0.1, 1e-5)
+    if res:
+        y2 = y2 + rr
+    if relu:
+        y2 = torch.relu(y2)
+    y2.backward(dy.float())
+    dx, dgamma, dbeta, dres = NV.bn_backward(dy, y, x, mean, invstd, g, relu, res)
+    # the relu mask is taken from the bf16 output, so allow a little slack
+    assert rel_err(dx, xr.grad) < 3e-2
+    assert rel_err(dgamma, gref.grad) < 2e-2
+    assert rel_err(dbeta, bref.grad) < 2e-2
+    if res:
+        assert rel_err(dres, rr.grad) < 2e-2
+
+
+def test_pools():
+    torch.manual_seed(5)
+    x = torch.randn(4, 32, 32, 64, device=dev()).bfloat16()
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    yref = F.max_pool2d(xr, 3, 2, 1)
+    y, arg = NV.maxpool_fwd(x)
+    assert torch.equal(y.float(), nhwc(yref))
+    dy = torch.randn_like(y)
+    yref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = NV.maxpool_bwd(dy, arg, x.shape)
+    assert rel_err(dx, nhwc(xr.grad)) < 1e-2
+    x2 = torch.randn(6, 7, 7, 2048, device=dev()).bfloat16()
+    ya = NV.avgpool_fwd(x2)
+    assert rel_err(ya, x2.float().mean(dim=(1, 2))) < 1e-2
+    dya = torch.randn_like(ya)
+    dxa = NV.avgpool_bwd(dya, x2.shape)
+    assert rel_err(dxa, (dya.float() / 49)[:, None, None, :].expand(6, 7, 7, 2048)) < 1e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_losses(dtype):
+    torch.manual_seed(6)
+    p = torch.randn(120, 1000, device=dev()).to(dtype)
+    t = torch.randn(120, 1000, device=dev()).to(dtype)
+    pr = p.float().requires_grad_(True)
+    lref = F.mse_loss(pr, t.float()); lref.backward()
+    loss, grad = NV.mse_loss_fwd_bwd(p, t)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert abs(loss.item() - lref.item()) < tol * max(1, abs(lref.item()))
+    assert rel_err(grad, pr.grad) < max(tol, 1e-5)
+    # second call on the same scratch must give the same answer (ticket counter reset)
+    loss2, _ = NV.mse_loss_fwd_bwd(p, t)
+    assert loss2.item() == loss.item()
+    s, g = NV.sum_loss_fwd_bwd(p)
+    assert abs(s.item() - p.float().sum().item()) < 1e-2 * p.numel() ** 0.5
+    assert torch.all(g.float() == 1)
+    probs = torch.softmax(torch.randn(120, 1000, device=dev()), -1)
+    pr2 = p.float().requires_grad_(True)
+    l2 = F.cross_entropy(pr2, probs); l2.backward()
+    l, g = NV.ce_prob_fwd_bwd(p, probs)
+    assert abs(l.item() - l2.item()) < 1e-3 * abs(l2.item()) + 1e-4
+    assert rel_err(g, pr2.grad) < max(tol, 1e-4)
+    labels = torch.randint(0, 1000, (120,), device=dev())
+    pr3 = p.float().requires_grad_(True)
+    l3 = F.cross_entropy(pr3, labels); l3.backward()
+    l, g = NV.ce_index_fwd_bwd(p, labels)
+    assert abs(l.item() - l3.item()) < 1e-3 * abs(l3.item()) + 1e-4
+    assert rel_err(g, pr3.grad) < max(tol, 1e-4)
+
+
+def test_ce_degenerate_single_class():
+    # /root/reference/ddp_gpus.py:37: cross_entropy on [B,1] logits with float targets is identically 0
+    out = torch.randn(32, 1, device=dev())
+    ys = torch.rand(32, 1, device=dev())
+    l, g = NV.ce_prob_fwd_bwd(out, ys)
+    assert l.item() == 0.0 and torch.all(g == 0)
+
+
+def test_layout_helpers():
+    x = torch.randn(3, 5, 17, 33, device=dev())
+    y = NV.nchw_to_nhwc_bf16(x)
+    assert torch.equal(y, x.permute(0, 2, 3, 1).contiguous().bfloat16())
+    a = torch.randn(100, 70, device=dev()).bfloat16()
+    assert torch.equal(NV.transpose_bf16(a), a.t().contiguous())
+    w = torch.randn(1001, device=dev())
+    assert torch.equal(NV.cast_bf16(w), w.bfloat16())
