@@ -169,8 +169,10 @@ coll_kernel(const __grid_constant__ CollArgs a) {
         float f[8];
         const int n = min(8, ch.len - g * 8);
         load8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, f);
+        if (a.scale != 1.f) {       // scale == 1 keeps the words bit-exact (raw broadcast of any dtype)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] *= a.scale;
+          for (int j = 0; j < 8; ++j) f[j] *= a.scale;
+        }
         if (kMode == kBcast) {
           // root pushes straight into every rank's staging (its own included)
           if (a.mc != nullptr) {

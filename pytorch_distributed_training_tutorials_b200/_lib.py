@@ -12,7 +12,31 @@ from typing import Optional
 import torch
 
 _lock = threading.Lock()
-_lib: Optional[C.CDLL] = None
+_lib: Optional["_Counted"] = None
+
+# Number of calls into the kernel library (each is one or more kernel launches of THIS library);
+# bench.py reports the per-step delta as "gpu_launches".
+launch_count = 0
+
+
+class _Counted:
+    """Attribute proxy over the CDLL handle that counts kernel-launching calls."""
+
+    def __init__(self, handle: C.CDLL, counted) -> None:
+        self._handle = handle
+        for name in counted:
+            setattr(self, name, self._wrap(getattr(handle, name)))
+
+    @staticmethod
+    def _wrap(fn):
+        def call(*args):
+            global launch_count
+            launch_count += 1
+            return fn(*args)
+        return call
+
+    def __getattr__(self, name):
+        return getattr(self._handle, name)
 
 vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint64
 
@@ -65,7 +89,7 @@ def available() -> bool:
     return lib_path().exists()
 
 
-def lib() -> C.CDLL:
+def lib() -> "_Counted":
     global _lib
     if _lib is not None:
         return _lib
@@ -94,8 +118,8 @@ def lib() -> C.CDLL:
         handle.b200dt_coll_chunk_bytes.argtypes = []
         handle.b200dt_device_sm_count.restype = i32
         handle.b200dt_version.restype = C.c_char_p
-        _lib = handle
-        return handle
+        _lib = _Counted(handle, [n for n in _SIGS if n != "b200dt_enable_peer_access"])
+        return _lib
 
 
 def check(rc: int, what: str = "") -> None:

@@ -1,0 +1,84 @@
+"""ResNet-50 on this library's sm_100a kernels (NHWC bf16 activations, fp32 master weights).
+
+Same topology, parameter names and parameter count (25 557 032) as torchvision's
+``ResNet(Bottleneck, [3, 4, 6, 3])`` that the reference subclasses at
+/root/reference/03.model_parallel.ipynb:807-833, so ``state_dict`` files are interchangeable.
+Differences are internal: every conv is the tcgen05 implicit GEMM, BN + ReLU (+ residual add) is
+one fused kernel pair, and activations never leave NHWC bf16 between the stem and the classifier.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+from torch import nn
+
+from ..ops import nn as bnn
+
+
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: bool = False) -> None:
+        super().__init__()
+        self.conv1 = bnn.Conv2d(inplanes, planes, 1)
+        self.bn1 = bnn.BatchNorm2d(planes, relu=True)
+        self.conv2 = bnn.Conv2d(planes, planes, 3, stride=stride)        # stride on the 3x3 (v1.5)
+        self.bn2 = bnn.BatchNorm2d(planes, relu=True)
+        self.conv3 = bnn.Conv2d(planes, planes * 4, 1)
+        self.bn3 = bnn.BatchNorm2d(planes * 4, relu=True)               # relu applied after the add
+        self.downsample: Optional[nn.Sequential] = None
+        if downsample:
+            self.downsample = nn.Sequential(
+                bnn.Conv2d(inplanes, planes * 4, 1, stride=stride),
+                bnn.BatchNorm2d(planes * 4, relu=False),
+            )
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        identity = x if self.downsample is None else self.downsample(x)
+        out = self.bn1(self.conv1(x))
+        out = self.bn2(self.conv2(out))
+        return self.bn3(self.conv3(out), residual=identity)
+
+
+class ResNet(nn.Module):
+    def __init__(self, layers: List[int], num_classes: int = 1000, zero_init_residual: bool = False) -> None:
+        super().__init__()
+        self.inplanes = 64
+        self.conv1 = bnn.StemConv(64)
+        self.bn1 = bnn.BatchNorm2d(64, relu=True)
+        self.maxpool = bnn.MaxPool3x3s2()
+        self.layer1 = self._make_layer(64, layers[0], 1)
+        self.layer2 = self._make_layer(128, layers[1], 2)
+        self.layer3 = self._make_layer(256, layers[2], 2)
+        self.layer4 = self._make_layer(512, layers[3], 2)
+        self.avgpool = bnn.GlobalAvgPool()
+        self.fc = bnn.Linear(512 * 4, num_classes, out_fp32=True)
+        if zero_init_residual:
+            for m in self.modules():
+                if isinstance(m, Bottleneck):
+                    nn.init.zeros_(m.bn3.weight)
+
+    def _make_layer(self, planes: int, blocks: int, stride: int) -> nn.Sequential:
+        need_ds = stride != 1 or self.inplanes != planes * 4
+        mods = [Bottleneck(self.inplanes, planes, stride, need_ds)]
+        self.inplanes = planes * 4
+        mods += [Bottleneck(self.inplanes, planes) for _ in range(1, blocks)]
+        return nn.Sequential(*mods)
+
+    def features_stage0(self, x: torch.Tensor) -> torch.Tensor:
+        """conv1 .. layer2 (the reference's ``seq1``, 03.model_parallel.ipynb:812-819)."""
+        x = self.maxpool(self.bn1(self.conv1(x)))
+        return self.layer2(self.layer1(x))
+
+    def features_stage1(self, x: torch.Tensor) -> torch.Tensor:
+        """layer3 .. avgpool (the reference's ``seq2``, 03.model_parallel.ipynb:821-825)."""
+        return self.avgpool(self.layer4(self.layer3(x)))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x: ``[N, 3, H, W]`` fp32 (NCHW, like torchvision) -> logits ``[N, num_classes]`` fp32."""
+        return self.fc(self.features_stage1(self.features_stage0(x)))
+
+
+def resnet50(num_classes: int = 1000, **kw) -> ResNet:
+    return ResNet([3, 4, 6, 3], num_classes=num_classes, **kw)

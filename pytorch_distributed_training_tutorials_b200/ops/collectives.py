@@ -1,0 +1,171 @@
+"""Symmetric-memory arena and launch helpers for the fused cross-GPU collectives.
+
+The arena is one peer-mapped staging buffer plus one signal pad per rank, obtained from
+``torch.distributed._symmetric_memory`` (cuMem + fabric handles + NVLS multicast binding are
+plumbing; the kernels that use the pointers are ours, ``csrc/allreduce.cu``).  ``TensorTable``
+turns a list of tensors (one DDP bucket) into the device-side pointer / chunk tables that a
+single ``b200dt_coll_launch`` consumes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .. import _lib
+from .._lib import check, lib, ptr, u64_array
+
+SIGNAL_WORDS = 8192
+MODE = {"oneshot": 0, "twoshot": 1, "nvls": 2, "bcast": 3}
+CHUNK_ELEMS = 16384
+ONESHOT_MAX_BYTES = 256 * 1024
+
+
+class SymmetricArena:
+    """Per-rank symmetric staging buffer + signal pad, mapped into every peer of the group."""
+
+    def __init__(self, nbytes: int, device: torch.device, group=None) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.device = device
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        if self.world > 8:
+            raise RuntimeError("the peer-memory collectives cover one NVSwitch domain (<= 8 GPUs)")
+        nbytes = (int(nbytes) + 4095) // 4096 * 4096
+        self.nbytes = nbytes
+        try:
+            symm_mem.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:
+            pass
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.sig = symm_mem.empty(SIGNAL_WORDS, dtype=torch.int32, device=device)
+        self.buf.zero_()
+        self.sig.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group=self.group)
+        self.sig_hdl = symm_mem.rendezvous(self.sig, group=self.group)
+        self.buf_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.sig_ptrs = [int(p) for p in self.sig_hdl.buffer_ptrs]
+        mc = 0
+        try:
+            if self.hdl.has_multicast_support():
+                mc = int(self.hdl.multicast_ptr)
+        except Exception:
+            mc = 0
+        self.multicast_ptr = mc
+        self._bufs_c = u64_array(self.buf_ptrs)
+        self._sigs_c = u64_array(self.sig_ptrs)
+        self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group, device_ids=[device.index])   # every pad is zero before first use
+
+    @property
+    def has_multicast(self) -> bool:
+        return self.multicast_ptr != 0
+
+    def check_status(self) -> None:
+        s = int(self.status.item())
+        if s:
+            raise RuntimeError(f"peer-memory collective timed out waiting for a peer (status {s}); "
+                               "a rank died or the ranks issued collectives in different orders")
+
+    def close(self) -> None:
+        self.hdl = self.sig_hdl = None
+        self.buf = self.sig = None
+
+
+def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> str:
+    if requested != "auto":
+        if requested == "nvls" and not arena.has_multicast:
+            raise RuntimeError("allreduce='nvls' requested but the arena has no multicast mapping")
+        return requested
+    if nbytes <= ONESHOT_MAX_BYTES:
+        return "oneshot"
+    return "nvls" if arena.has_multicast else "twoshot"
+
+
+class TensorTable:
+    """Device-side {ptr, numel} + chunk tables for a fixed list of same-dtype tensors."""
+
+    def __init__(self, numels: Sequence[int], device: torch.device, wire_bf16: bool, tensor_bf16: bool = False) -> None:
+        self.device = device
+        self.numels = [int(n) for n in numels]
+        self.tensor_bf16 = tensor_bf16
+        self.wire_bf16 = wire_bf16 or tensor_bf16
+        rows = []
+        off = 0
+        for ti, n in enumerate(self.numels):
+            s = 0
+            while s < n:
+                ln = min(CHUNK_ELEMS, n - s)
+                rows.append((ti, s, ln, off))
+                off += (ln + 7) // 8 * 8
+                s += ln
+        self.stage_elems = off
+        self.stage_bytes = off * (2 if self.wire_bf16 else 4)
+        self.n_chunks = len(rows)
+        assert lib().b200dt_coll_chunk_bytes() == 24
+        raw = torch.empty(max(len(rows), 1) * 3, dtype=torch.int64)
+        for i, (ti, s, ln, o) in enumerate(rows):
+            raw[3 * i] = (s << 32) | ti                 # little-endian: {int32 tensor, int32 start}
+            raw[3 * i + 1] = ln                          # {int32 len, int32 pad}
+            raw[3 * i + 2] = o
+        self.chunks = raw.to(device)
+        self._host = torch.empty(len(self.numels) * 2, dtype=torch.int64).pin_memory() \
+            if torch.cuda.is_available() else torch.empty(len(self.numels) * 2, dtype=torch.int64)
+        self.tensors = torch.zeros(len(self.numels) * 2, dtype=torch.int64, device=device)
+        self._ptr_key = None
+
+    def grid(self, max_blocks: int) -> int:
+        return max(1, min(max_blocks, self.n_chunks))
+
+    def bind(self, tensors: Sequence[torch.Tensor], stream: torch.cuda.Stream) -> None:
+        """Point the table at these tensors (skips the upload when the addresses did not change)."""
+        key = tuple(t.data_ptr() for t in tensors)
+        if key == self._ptr_key:
+            return
+        for i, t in enumerate(tensors):
+            assert t.numel() == self.numels[i] and t.is_contiguous()
+            self._host[2 * i] = t.data_ptr()
+            self._host[2 * i + 1] = t.numel()
+        with torch.cuda.stream(stream):
+            self.tensors.copy_(self._host, non_blocking=True)
+        self._ptr_key = key
+
+
+def launch(mode: str, arena: SymmetricArena, table: TensorTable, scale: float, stream: torch.cuda.Stream,
+           root: int = 0, sig_base: int = 0, max_blocks: int = 32) -> None:
+    grid = table.grid(max_blocks)
+    if table.stage_bytes > arena.nbytes:
+        raise RuntimeError(f"bucket of {table.stage_bytes} bytes does not fit the {arena.nbytes}-byte arena")
+    with torch.cuda.device(arena.device):
+        check(lib().b200dt_coll_launch(MODE[mode], arena._bufs_c, arena._sigs_c, arena.multicast_ptr if mode in ("nvls", "bcast") else 0,
+                                       arena.rank, arena.world, root, ptr(table.tensors), ptr(table.chunks),
+                                       table.n_chunks, 0, int(table.tensor_bf16), int(table.wire_bf16), scale,
+                                       sig_base, grid, ptr(arena.status), stream.cuda_stream), f"coll_launch[{mode}]")
+
+
+def all_reduce_(tensors: List[torch.Tensor], arena: SymmetricArena, mode: str = "auto", scale: float = 1.0,
+                wire_bf16: bool = False, stream: Optional[torch.cuda.Stream] = None, max_blocks: int = 32) -> None:
+    """In-place sum (times ``scale``) of same-dtype CUDA tensors across the arena's group."""
+    dev = arena.device
+    stream = stream or torch.cuda.current_stream(dev)
+    tb16 = tensors[0].dtype == torch.bfloat16
+    table = TensorTable([t.numel() for t in tensors], dev, wire_bf16, tb16)
+    table.bind(tensors, stream)
+    m = pick_mode(table.stage_bytes, arena, mode)
+    launch(m, arena, table, scale, stream, max_blocks=max_blocks)
+
+
+def broadcast_(tensors: List[torch.Tensor], arena: SymmetricArena, root: int = 0,
+               stream: Optional[torch.cuda.Stream] = None, max_blocks: int = 32) -> None:
+    """In-place broadcast of fp32 / bf16 CUDA tensors from ``root`` through peer stores."""
+    dev = arena.device
+    stream = stream or torch.cuda.current_stream(dev)
+    tb16 = tensors[0].dtype == torch.bfloat16
+    table = TensorTable([t.numel() for t in tensors], dev, False, tb16)
+    table.bind(tensors, stream)
+    launch("bcast", arena, table, 1.0, stream, root=root, max_blocks=max_blocks)

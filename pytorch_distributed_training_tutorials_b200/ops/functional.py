@@ -1,0 +1,248 @@
+"""Differentiable ops on top of the sm_100a kernels (``torch.autograd.Function`` per op).
+
+Conventions: activations are NHWC bf16 tensors ``[N, H, W, C]``; parameters are fp32 masters
+(what the optimizer and DDP see) and are cast to bf16 operands on the fly; weight gradients come
+back in fp32 straight from the tensor-core accumulators.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import native as NV
+
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _shadow(w: torch.Tensor) -> torch.Tensor:
+    """bf16 operand copy of an fp32 master weight, cached until the master changes."""
+    cache = getattr(w, "_b200_shadow", None)
+    ver = w._version
+    if cache is not None and cache[0] == ver and cache[1].device == w.device:
+        return cache[1]
+    s = NV.cast_bf16(w.detach().contiguous())
+    try:
+        w._b200_shadow = (ver, s)
+    except Exception:  # pragma: no cover - tensors that refuse attributes
+        pass
+    return s
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu, out_fp32):
+        wb = _shadow(weight)
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.dtype != BF16:
+            x2 = x2.to(BF16)
+        x2 = x2.contiguous()
+        y = NV.gemm_tn(x2, wb, bias=bias.detach() if bias is not None else None, relu=relu,
+                       out_dtype=F32 if out_fp32 else BF16)
+        ctx.save_for_backward(x2, weight, y if relu else None)
+        ctx.has_bias = bias is not None
+        ctx.relu = relu
+        ctx.x_shape = x.shape
+        ctx.x_dtype = x.dtype
+        return y.view(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, y = ctx.saved_tensors
+        N, Kf = weight.shape
+        dy2 = dy.reshape(-1, N)
+        if ctx.relu:
+            dy2 = dy2 * (y > 0)
+        dyb = dy2.to(BF16).contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            wt = NV.transpose_bf16(_shadow(weight))            # [K, N]: K-major operand for dgrad
+            if N % 8 == 0:
+                dx = NV.gemm_tn(dyb, wt).view(ctx.x_shape).to(ctx.x_dtype)
+            else:
+                dx = (dy2.float() @ weight.detach()).view(ctx.x_shape).to(ctx.x_dtype)
+        if ctx.needs_input_grad[1]:
+            if N % 8 == 0 and Kf % 8 == 0:
+                dw = NV.gemm_nt_reduce(dyb, x2)
+            else:
+                dw = dy2.float().t() @ x2.float()
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy2.float().sum(0)
+        return dx, dw, db, None, None
+
+
+def linear(x, weight, bias=None, relu: bool = False, out_fp32: bool = False):
+    """y = x @ weight^T + bias on tcgen05; needs in_features % 8 == 0 (TMA row pitch)."""
+    return _Linear.apply(x, weight, bias, relu, out_fp32)
+
+
+class _Conv2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, stride):
+        wb = _shadow(weight)
+        y = NV.conv2d_fprop(x, wb, stride=stride)
+        ctx.save_for_backward(x, weight)
+        ctx.stride = stride
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        R = weight.shape[1]
+        dy = dy.contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            wt = NV.filter_transpose(_shadow(weight), stride=ctx.stride)
+            dx = NV.conv2d_dgrad(dy, wt, x.shape, R, stride=ctx.stride)
+        if ctx.needs_input_grad[1]:
+            dw = NV.conv2d_wgrad(x, dy, R, stride=ctx.stride)
+        return dx, dw, None
+
+
+def conv2d(x, weight, stride: int = 1):
+    """NHWC conv, weight ``[Cout, R, R, Cin]``, R in {1,3}, pad R//2, stride in {1,2}."""
+    return _Conv2d.apply(x, weight, stride)
+
+
+class _StemConv(torch.autograd.Function):
+    """7x7 stride-2 pad-3 convolution of the fp32 NCHW network input (Cin = 3)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        NB, _, H, W = x.shape
+        cols = NV.stem_im2col(x.contiguous())
+        wk = torch.zeros((weight.shape[0], NV.STEM_LDK), device=x.device, dtype=BF16)
+        wk[:, :147] = weight.detach().reshape(weight.shape[0], 147)
+        y = NV.gemm_tn(cols, wk)
+        ctx.save_for_backward(x, weight)
+        return y.view(NB, H // 2, W // 2, weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        dw = None
+        if ctx.needs_input_grad[1]:
+            cols = NV.stem_im2col(x.contiguous())            # recomputed: cheaper than keeping it
+            dy2 = dy.reshape(-1, weight.shape[0]).contiguous()
+            dwk = NV.gemm_nt_reduce(dy2, cols)               # [64, 160]
+            dw = dwk[:, :147].reshape(weight.shape).contiguous()
+        return None, dw
+
+
+def stem_conv(x_nchw_f32, weight):
+    """weight ``[64, 7, 7, 3]`` (OHWI)."""
+    return _StemConv.apply(x_nchw_f32, weight)
+
+
+class _BatchNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training):
+        shp = x.shape
+        Cc = shp[-1]
+        x2 = x.reshape(-1, Cc)
+        r2 = residual.reshape(-1, Cc) if residual is not None else None
+        if training:
+            sums = NV.bn_stats(x2)
+            y, mean, invstd = NV.bn_apply(x2, r2, sums, gamma.detach(), beta.detach(), running_mean,
+                                          running_var, eps, momentum, relu)
+        else:
+            y = NV.bn_apply_eval(x2, r2, gamma.detach(), beta.detach(), running_mean, running_var, eps, relu)
+            mean = running_mean
+            invstd = torch.rsqrt(running_var + eps)
+        ctx.save_for_backward(x2, y, gamma, mean, invstd)
+        ctx.relu = relu
+        ctx.has_res = residual is not None
+        ctx.shape = shp
+        ctx.training = training
+        return y.view(shp)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, y, gamma, mean, invstd = ctx.saved_tensors
+        Cc = ctx.shape[-1]
+        dy2 = dy.reshape(-1, Cc).contiguous()
+        if not ctx.training:
+            raise RuntimeError("backward through eval-mode BatchNorm is not supported")
+        want_res = ctx.has_res and ctx.needs_input_grad[3]
+        dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res)
+        return (dx.view(ctx.shape), dgamma, dbeta, dres.view(ctx.shape) if dres is not None else None,
+                None, None, None, None, None, None)
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, residual=None, eps: float = 1e-5,
+               momentum: float = 0.1, relu: bool = False, training: bool = True):
+    """y = act(BN(x) + residual) with batch statistics; updates running stats in place."""
+    return _BatchNorm.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training)
+
+
+class _MaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y, arg = NV.maxpool_fwd(x.contiguous())
+        ctx.save_for_backward(arg)
+        ctx.shape = x.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (arg,) = ctx.saved_tensors
+        return NV.maxpool_bwd(dy.contiguous(), arg, ctx.shape)
+
+
+def max_pool_3x3_s2(x):
+    return _MaxPool.apply(x)
+
+
+class _AvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.shape = x.shape
+        return NV.avgpool_fwd(x.contiguous())
+
+    @staticmethod
+    def backward(ctx, dy):
+        return NV.avgpool_bwd(dy.contiguous(), ctx.shape)
+
+
+def global_avg_pool(x):
+    """[N,H,W,C] -> [N,C]."""
+    return _AvgPool.apply(x)
+
+
+class _Loss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, kind, pred, target):
+        pred_c = pred.contiguous()
+        want = pred.requires_grad
+        if kind == "mse":
+            loss, grad = NV.mse_loss_fwd_bwd(pred_c, target, 1.0, want)
+        elif kind == "sum":
+            loss, grad = NV.sum_loss_fwd_bwd(pred_c, 1.0, want)
+        elif kind == "ce_prob":
+            loss, grad = NV.ce_prob_fwd_bwd(pred_c, target, 1.0, want)
+        else:
+            loss, grad = NV.ce_index_fwd_bwd(pred_c, target, 1.0, want)
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return None, (grad * g.to(grad.dtype)) if grad is not None else None, None
+
+
+def mse_loss(pred, target):
+    return _Loss.apply("mse", pred, target)
+
+
+def sum_loss(x):
+    return _Loss.apply("sum", x, None)
+
+
+def cross_entropy(logits, target):
+    """Mean cross entropy; ``target`` is either class indices (int64 ``[B]``) or probabilities
+    (float, same shape as ``logits``, the form the reference uses at ddp_gpus.py:37)."""
+    if target.dtype in (torch.int64, torch.int32):
+        return _Loss.apply("ce_index", logits, target)
+    return _Loss.apply("ce_prob", logits, target)

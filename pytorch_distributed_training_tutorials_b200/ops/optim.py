@@ -1,0 +1,204 @@
+"""Fused multi-tensor optimizers.
+
+``FusedSGD`` / ``FusedAdam`` are drop-in ``torch.optim.Optimizer`` subclasses with the hyper-
+parameters the reference uses (SGD without momentum: /root/reference/ddp_gpus.py:82,
+03.model_parallel.ipynb:534,977; Adam defaults: 01.data_parallel.ipynb:287).  On CUDA one kernel
+launch per device updates every parameter, refreshes the bf16 operand shadows used by the tcgen05
+kernels and can clear the gradients in the same pass; parameters may live on several devices
+(the model-parallel case: one optimizer over ``cuda:0`` and ``cuda:1`` parameters).
+On CPU tensors the same math runs through plain torch ops.
+"""
+from __future__ import annotations
+
+from typing import Dict, List
+
+import torch
+from torch.optim import Optimizer
+
+from .. import _lib
+from .._lib import check, lib, ptr, stream_ptr
+
+CHUNK = 8192
+
+
+class _DeviceTable:
+    """Device-resident {param, grad, shadow, numel, m, v} rows + the chunk list for one device."""
+
+    def __init__(self, device: torch.device) -> None:
+        self.device = device
+        self.key = None
+        self.meta = None
+        self.chunks = None
+        self.n_chunks = 0
+
+    def update(self, rows: List[List[int]]) -> None:
+        key = tuple(tuple(r) for r in rows)
+        if key == self.key:
+            return
+        meta = torch.tensor(rows, dtype=torch.int64)
+        ch = []
+        for ti, r in enumerate(rows):
+            n = r[3]
+            ch.extend((ti, s) for s in range(0, n, CHUNK))
+        chunks = torch.tensor(ch, dtype=torch.int32)
+        self.meta = meta.to(self.device, non_blocking=False)
+        self.chunks = chunks.to(self.device, non_blocking=False)
+        self.n_chunks = len(ch)
+        self.key = key
+
+
+class _FusedBase(Optimizer):
+    def __init__(self, params, defaults, fuse_zero_grad: bool, bf16_shadow: bool):
+        super().__init__(params, defaults)
+        self.fuse_zero_grad = fuse_zero_grad
+        self.bf16_shadow = bf16_shadow
+        self._tables: Dict[tuple, _DeviceTable] = {}
+        self._shadows: Dict[int, torch.Tensor] = {}     # kept out of .state: state_dict stays torch-compatible
+        self._grads_cleared = False
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        if self.fuse_zero_grad and self._grads_cleared:
+            # the last step() already zeroed every gradient in place
+            self._grads_cleared = False
+            return
+        super().zero_grad(set_to_none=set_to_none)
+
+    def _shadow_for(self, p: torch.Tensor):
+        if not self.bf16_shadow or p.dim() < 2:
+            return None
+        sh = self._shadows.get(id(p))
+        if sh is None or sh.device != p.device or sh.shape != p.shape:
+            from . import native as NV
+            sh = NV.cast_bf16(p.detach().contiguous())
+            self._shadows[id(p)] = sh
+        return sh
+
+    def _cuda_groups(self, group):
+        """params with grads of this param group, split by device."""
+        by_dev: Dict[torch.device, List[torch.Tensor]] = {}
+        cpu: List[torch.Tensor] = []
+        for p in group["params"]:
+            if p.grad is None:
+                continue
+            if p.grad.is_sparse:
+                raise RuntimeError("sparse gradients are not supported")
+            if p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and p.grad.is_contiguous() \
+                    and p.grad.dtype == torch.float32:
+                by_dev.setdefault(p.device, []).append(p)
+            else:
+                cpu.append(p)
+        return by_dev, cpu
+
+    def _publish_shadows(self, params) -> None:
+        for p in params:
+            sh = self._shadows.get(id(p))
+            if sh is not None:
+                p._b200_shadow = (p._version, sh)
+
+
+class FusedSGD(_FusedBase):
+    """SGD without momentum (optionally with weight decay): ``p -= lr * (g + wd * p)``."""
+
+    def __init__(self, params, lr: float = 1e-3, weight_decay: float = 0.0, fuse_zero_grad: bool = False,
+                 bf16_shadow: bool = True) -> None:
+        if lr < 0:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        super().__init__(params, dict(lr=lr, weight_decay=weight_decay), fuse_zero_grad, bf16_shadow)
+
+    @torch.no_grad()
+    def step(self, closure=None, grad_scale: float = 1.0):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for gi, group in enumerate(self.param_groups):
+            by_dev, slow = self._cuda_groups(group)
+            for dev, ps in by_dev.items():
+                rows = []
+                for p in ps:
+                    sh = self._shadow_for(p)
+                    rows.append([p.data_ptr(), p.grad.data_ptr(), sh.data_ptr() if sh is not None else 0,
+                                 p.numel(), 0, 0, 0, 0])
+                tab = self._tables.setdefault((gi, dev), _DeviceTable(dev))
+                tab.update(rows)
+                with torch.cuda.device(dev):
+                    check(lib().b200dt_multi_sgd(ptr(tab.meta), ptr(tab.chunks), tab.n_chunks, group["lr"],
+                                                 group["weight_decay"], grad_scale, int(self.fuse_zero_grad),
+                                                 stream_ptr(dev)), "multi_sgd")
+                self._publish_shadows(ps)
+            for p in slow:
+                g = p.grad * grad_scale if grad_scale != 1.0 else p.grad
+                if group["weight_decay"]:
+                    g = g.add(p, alpha=group["weight_decay"])
+                p.add_(g, alpha=-group["lr"])
+                if self.fuse_zero_grad:
+                    p.grad.zero_()
+        self._grads_cleared = self.fuse_zero_grad
+        return loss
+
+
+class FusedAdam(_FusedBase):
+    """Adam (Kingma & Ba) with torch's default update rule (no amsgrad)."""
+
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, fuse_zero_grad: bool = False, bf16_shadow: bool = True) -> None:
+        if lr < 0:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay),
+                         fuse_zero_grad, bf16_shadow)
+
+    @torch.no_grad()
+    def step(self, closure=None, grad_scale: float = 1.0):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for gi, group in enumerate(self.param_groups):
+            b1, b2 = group["betas"]
+            t = None
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                if "step" not in st:
+                    st["step"] = torch.tensor(0.0)
+                st["step"] += 1
+                t = int(st["step"].item()) if t is None else t
+            if t is None:
+                continue
+            by_dev, slow = self._cuda_groups(group)
+            for dev, ps in by_dev.items():
+                rows = []
+                for p in ps:
+                    st = self.state[p]
+                    if "exp_avg" not in st:
+                        st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                        st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    sh = self._shadow_for(p)
+                    rows.append([p.data_ptr(), p.grad.data_ptr(), sh.data_ptr() if sh is not None else 0,
+                                 p.numel(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), 0, 0])
+                tab = self._tables.setdefault((gi, dev), _DeviceTable(dev))
+                tab.update(rows)
+                with torch.cuda.device(dev):
+                    check(lib().b200dt_multi_adam(ptr(tab.meta), ptr(tab.chunks), tab.n_chunks, group["lr"], b1,
+                                                  b2, group["eps"], group["weight_decay"], t, grad_scale,
+                                                  int(self.fuse_zero_grad), stream_ptr(dev)), "multi_adam")
+                self._publish_shadows(ps)
+            for p in slow:
+                st = self.state[p]
+                if "exp_avg" not in st:
+                    st["exp_avg"] = torch.zeros_like(p)
+                    st["exp_avg_sq"] = torch.zeros_like(p)
+                g = p.grad * grad_scale if grad_scale != 1.0 else p.grad
+                if group["weight_decay"]:
+                    g = g.add(p, alpha=group["weight_decay"])
+                st["exp_avg"].mul_(b1).add_(g, alpha=1 - b1)
+                st["exp_avg_sq"].mul_(b2).addcmul_(g, g, value=1 - b2)
+                bc1 = 1 - b1 ** t
+                bc2 = 1 - b2 ** t
+                denom = (st["exp_avg_sq"].sqrt() / (bc2 ** 0.5)).add_(group["eps"])
+                p.addcdiv_(st["exp_avg"], denom, value=-group["lr"] / bc1)
+                if self.fuse_zero_grad:
+                    p.grad.zero_()
+        self._grads_cleared = self.fuse_zero_grad
+        return loss

@@ -1,0 +1,332 @@
+"""``DistributedDataParallel``: multi-process data parallelism, one process per GPU.
+
+Same construction-time and per-step contract as the wrapper the reference uses at
+/root/reference/ddp_gpus.py:32 (``DDP(model, device_ids=[gpu_id])``, all defaults):
+
+* ctor: parameter shapes are verified across ranks, then rank 0's parameters and buffers are
+  broadcast so that every replica starts identical;
+* forward: buffers (BatchNorm running statistics) are re-broadcast from rank 0 when
+  ``broadcast_buffers`` is set, the wrapped module runs, and the C++ reducer is armed;
+* backward: one autograd post-hook per parameter; when the last gradient of a bucket is ready the
+  bucket is reduced *while backward keeps running*: on GPUs by ONE fused sm_100a kernel on a side
+  stream (gather grads -> 1/world scale -> wire-dtype cast -> one-shot / two-shot / NVLS reduce
+  over NVLink peer memory -> result written straight into ``.grad``), on CPU / gloo by
+  ``dist.all_reduce`` on a flat bucket;
+* first iteration uses one bucket holding everything, then buckets are rebuilt in the observed
+  gradient-ready order with the 1 MiB / ``bucket_cap_mb`` caps, rank 0's layout being authoritative;
+* ``no_sync()`` skips the reduction for gradient accumulation; ``state_dict()`` keys carry the
+  ``module.`` prefix exactly like torch's wrapper.
+"""
+from __future__ import annotations
+
+import contextlib
+import sys
+import time
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from .. import group as _group
+from ._native_reducer import load as _load_reducer
+
+FIRST_BUCKET_BYTES = 1024 * 1024
+
+
+class _Bucket:
+    def __init__(self, index: int, param_ids: List[int]) -> None:
+        self.index = index
+        self.param_ids = param_ids
+        self.table = None          # ops.collectives.TensorTable (GPU path)
+        self.flat = None           # flat buffer (fallback path)
+        self.work = None
+        self.nbytes = 0
+        self.mode = None
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids: Optional[List[int]] = None, output_device=None,
+                 broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: float = 25.0,
+                 find_unused_parameters: bool = False, gradient_as_bucket_view: bool = False,
+                 init_sync: bool = True, allreduce: str = "auto", comm_dtype: str = "fp32",
+                 max_comm_blocks: int = 32) -> None:
+        super().__init__()
+        if find_unused_parameters:
+            raise NotImplementedError("find_unused_parameters=True is not supported (the reference never uses it)")
+        if not dist.is_initialized():
+            raise RuntimeError("Default process group has not been initialized, please make sure to call "
+                               "init() / init_process_group.")
+        self.module = module
+        self.process_group = process_group if process_group is not None else dist.group.WORLD
+        self.world_size = dist.get_world_size(self.process_group)
+        self.rank = dist.get_rank(self.process_group)
+        self.broadcast_buffers = broadcast_buffers
+        self.bucket_bytes_cap = int(bucket_cap_mb * 1024 * 1024)
+        self.require_backward_grad_sync = True
+        self.allreduce = allreduce
+        self.comm_dtype = comm_dtype
+        self.max_comm_blocks = max_comm_blocks
+        self.gradient_as_bucket_view = gradient_as_bucket_view
+
+        self._params = [p for p in module.parameters() if p.requires_grad]
+        if not self._params:
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any parameter "
+                               "that requires a gradient.")
+        devs = {p.device for p in self._params}
+        if len(devs) != 1:
+            raise ValueError("DistributedDataParallel expects all parameters on one device "
+                             f"(found {sorted(map(str, devs))}); multi-device modules belong to parallel.model_parallel")
+        self.device = next(iter(devs))
+        if device_ids is not None:
+            if len(device_ids) != 1:
+                raise ValueError("device_ids can only be None or contain a single element.")
+            d = device_ids[0]
+            d = torch.device("cuda", d) if isinstance(d, int) else torch.device(d)
+            if d != self.device:
+                raise ValueError(f"module parameters live on {self.device} but device_ids={device_ids}")
+        self.device_ids = device_ids
+        self.output_device = output_device
+        self._use_kernels = (self.device.type == "cuda" and self.world_size > 1 and allreduce != "nccl"
+                             and all(p.dtype in (torch.float32, torch.bfloat16) for p in self._params))
+        self._arena = None
+        self._side_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._ready_event = torch.cuda.Event() if self.device.type == "cuda" else None
+        self._fallback_reason = None
+
+        if init_sync and self.world_size > 1:
+            self._verify_params_across_ranks()
+        if self._use_kernels:
+            self._create_arena()
+        if init_sync and self.world_size > 1:
+            self._sync_module_states()
+
+        R = _load_reducer()
+        self._R = R
+        # iteration 1: one bucket holding every parameter (launch once, learn the ready order)
+        self._rebuilt = False
+        first = [list(range(len(self._params)))]
+        self._buckets = self._make_buckets(first)
+        self._reducer = R.Reducer(self._params, first, self._on_bucket_ready, self._on_finalize)
+        self._reducer.set_record_order(True)
+        self._stats = {"allreduce_bytes": 0, "launches": 0, "rebuilds": 0}
+        self._t_ctor = time.time()
+
+    # ------------------------------------------------------------------ construction helpers
+    def _verify_params_across_ranks(self) -> None:
+        """Every rank must hold the same number of parameters with the same shapes (X1)."""
+        desc = [tuple(p.shape) for p in self._params]
+        h = hash(tuple(desc)) & 0x7FFFFFFFFFFFFFFF
+        mine = torch.tensor([len(desc), h, sum(p.numel() for p in self._params)], dtype=torch.int64,
+                            device=self.device if self.device.type == "cuda" else "cpu")
+        allv = [torch.zeros_like(mine) for _ in range(self.world_size)]
+        dist.all_gather(allv, mine, group=self.process_group)
+        for r, v in enumerate(allv):
+            if not torch.equal(v.cpu(), mine.cpu()):
+                raise RuntimeError(
+                    f"DDP expects same model across all ranks, but Rank {self.rank} has {int(mine[0])} params "
+                    f"({int(mine[2])} elements), while rank {r} has {int(v[0])} params ({int(v[2])} elements).")
+
+    def _create_arena(self) -> None:
+        from ..ops.collectives import SymmetricArena
+        st = _group.state() if _group.is_initialized() or dist.is_initialized() else None
+        total = sum((p.numel() + 7) // 8 * 8 * 4 for p in self._params)
+        # the construction-time broadcast stages parameters AND buffers (as 32-bit words) at once
+        bufs = sum((b.numel() * b.element_size() // 4 + 8) // 8 * 8 * 4 for b in self.module.buffers())
+        need = total + bufs + (1 << 20)
+        try:
+            if st is not None and st.arena is not None and st.arena.nbytes >= need \
+                    and st.arena.group is self.process_group:
+                self._arena = st.arena
+            else:
+                self._arena = SymmetricArena(need, self.device, self.process_group)
+                if st is not None and st.arena is None:
+                    st.arena = self._arena
+        except Exception as e:  # symmetric memory unavailable: say so loudly, fall back to NCCL
+            self._use_kernels = False
+            self._fallback_reason = f"{type(e).__name__}: {e}"
+            print(f"[b200dt] WARNING rank {self.rank}: symmetric-memory arena unavailable ({self._fallback_reason}); "
+                  "gradient all-reduce falls back to NCCL", file=sys.stderr, flush=True)
+        flag = torch.tensor([1 if self._use_kernels else 0], device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.process_group)
+        if int(flag.item()) == 0:
+            self._use_kernels = False
+
+    def _broadcast_tensors(self, tensors: List[torch.Tensor]) -> None:
+        """Rank 0's values overwrite everybody's. On GPUs every tensor whose byte size is a multiple
+        of 4 rides ONE peer-store kernel as raw 32-bit words (bit-exact for any dtype)."""
+        if not tensors:
+            return
+        fast, slow = [], []
+        for t in tensors:
+            if (self._use_kernels and t.is_cuda and t.is_contiguous() and t.numel() > 0
+                    and (t.numel() * t.element_size()) % 4 == 0 and t.data_ptr() % 4 == 0):
+                fast.append(t.view(-1).view(torch.int32) if t.dtype != torch.float32 else t.view(-1))
+            elif t.numel() > 0:
+                slow.append(t)
+        if fast:
+            from ..ops import collectives as coll
+            cur = torch.cuda.current_stream(self.device)
+            key = tuple(t.numel() for t in fast)
+            tables = self.__dict__.setdefault("_bcast_tables", {})
+            table = tables.get(key)
+            if table is None:
+                table = coll.TensorTable(list(key), self.device, False, False)
+                tables[key] = table
+            table.bind(fast, cur)
+            coll.launch("bcast", self._arena, table, 1.0, cur, root=0, sig_base=4096,
+                        max_blocks=self.max_comm_blocks)
+        if slow:
+            src = dist.get_global_rank(self.process_group, 0)
+            by_dtype = {}
+            for t in slow:
+                by_dtype.setdefault((t.dtype, t.device), []).append(t)
+            for ts in by_dtype.values():          # coalesced: one broadcast per dtype
+                flat = torch.cat([t.reshape(-1) for t in ts])
+                dist.broadcast(flat, src=src, group=self.process_group)
+                off = 0
+                for t in ts:
+                    n = t.numel()
+                    t.copy_(flat[off:off + n].view_as(t))
+                    off += n
+
+    def _sync_module_states(self) -> None:
+        """Rank 0's parameters and buffers overwrite everybody else's (X2)."""
+        with torch.no_grad():
+            self._broadcast_tensors([p.data for p in self.module.parameters()] + [b.data for b in self.module.buffers()])
+
+    def _sync_buffers(self) -> None:
+        """Per-forward buffer broadcast from rank 0 (X3)."""
+        bufs = [b.data for b in self.module.buffers()]
+        if bufs:
+            with torch.no_grad():
+                self._broadcast_tensors(bufs)
+
+    def _make_buckets(self, layout: List[List[int]]) -> List[_Bucket]:
+        out = []
+        for i, ids in enumerate(layout):
+            b = _Bucket(i, list(ids))
+            b.nbytes = sum(self._params[j].numel() * self._params[j].element_size() for j in ids)
+            if self._use_kernels:
+                from ..ops import collectives as coll
+                tb16 = self._params[ids[0]].dtype == torch.bfloat16
+                b.table = coll.TensorTable([self._params[j].numel() for j in ids], self.device,
+                                           self.comm_dtype == "bf16", tb16)
+                b.mode = coll.pick_mode(b.table.stage_bytes, self._arena, self.allreduce)
+            out.append(b)
+        return out
+
+    def _rebuild_buckets(self) -> None:
+        """Re-bucket in gradient-ready order with caps [1 MiB, bucket_cap]; rank 0 decides."""
+        order = list(self._reducer.ready_order())
+        if len(order) != len(self._params):
+            return
+        if self.world_size > 1:
+            t = torch.tensor(order, dtype=torch.int64, device=self.device if self.device.type == "cuda" else "cpu")
+            dist.broadcast(t, src=0, group=self.process_group)
+            order = t.cpu().tolist()
+        tensors = [self._params[i] for i in order]
+        layout, _ = self._R.assign_buckets(tensors, [FIRST_BUCKET_BYTES, self.bucket_bytes_cap], order)
+        self._buckets = self._make_buckets(layout)
+        self._reducer.set_buckets(layout)
+        self._reducer.set_record_order(False)
+        self._rebuilt = True
+        self._stats["rebuilds"] += 1
+
+    # ------------------------------------------------------------------ reducer callbacks
+    def _on_bucket_ready(self, bi: int) -> None:
+        b = self._buckets[bi]
+        if self.world_size == 1:
+            return
+        grads = []
+        for j in b.param_ids:
+            g = self._params[j].grad
+            if g is None:
+                raise RuntimeError(f"parameter {j} has no gradient at bucket launch")
+            grads.append(g if g.is_contiguous() else g.contiguous())
+        self._stats["allreduce_bytes"] += b.nbytes
+        self._stats["launches"] += 1
+        if self._use_kernels:
+            from ..ops import collectives as coll
+            cur = torch.cuda.current_stream(self.device)
+            self._ready_event.record(cur)
+            self._side_stream.wait_event(self._ready_event)
+            for g in grads:
+                g.record_stream(self._side_stream)
+            b.table.bind(grads, self._side_stream)
+            coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
+                        max_blocks=self.max_comm_blocks)
+        else:
+            # gloo / NCCL path: flat bucket, pre-scale, async all-reduce (what torch's Reducer does)
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            if self.comm_dtype == "bf16" and flat.dtype == torch.float32 and flat.is_cuda:
+                flat = flat.to(torch.bfloat16)
+            flat.div_(self.world_size)
+            b.flat = flat
+            b.grads = grads
+            b.work = dist.all_reduce(flat, group=self.process_group, async_op=True)
+
+    def _on_finalize(self) -> None:
+        if self.world_size == 1:
+            return
+        if self._use_kernels:
+            torch.cuda.current_stream(self.device).wait_stream(self._side_stream)
+        else:
+            for b in self._buckets:
+                if b.work is None:
+                    continue
+                b.work.wait()
+                off = 0
+                for g, j in zip(b.grads, b.param_ids):
+                    n = g.numel()
+                    piece = b.flat[off:off + n].view_as(g)
+                    p = self._params[j]
+                    if p.grad is g:
+                        g.copy_(piece)
+                    else:
+                        p.grad = piece.to(p.dtype).clone()
+                    off += n
+                b.work = None
+                b.flat = None
+                b.grads = None
+
+    # ------------------------------------------------------------------ nn.Module API
+    def forward(self, *inputs, **kwargs):
+        with torch.autograd.profiler.record_function("b200dt.DistributedDataParallel.forward"):
+            sync = torch.is_grad_enabled() and self.require_backward_grad_sync
+            if sync and not self._rebuilt and self._reducer.finalized() and len(self._reducer.ready_order()) == len(self._params):
+                self._rebuild_buckets()
+            if self.world_size > 1 and self.broadcast_buffers and self.require_backward_grad_sync:
+                self._sync_buffers()
+            out = self.module(*inputs, **kwargs)
+            if sync:
+                self._reducer.prepare_for_backward()
+            return out
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Skip gradient synchronisation inside the context (gradients accumulate locally)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        self._reducer.set_require_sync(False)
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+            self._reducer.set_require_sync(old)
+
+    def get_logging_data(self) -> dict:
+        d = dict(self._reducer.stats())
+        d.update(self._stats)
+        d.update(world_size=self.world_size, rank=self.rank, rebuilt=self._rebuilt,
+                 bucket_sizes_mib=[round(b.nbytes / 2**20, 2) for b in self._buckets],
+                 bucket_modes=[b.mode for b in self._buckets],
+                 comm="b200dt-peer-memory" if self._use_kernels else (dist.get_backend(self.process_group) if self.world_size > 1 else "none"),
+                 comm_dtype=self.comm_dtype, fallback_reason=self._fallback_reason,
+                 multicast=bool(self._arena.has_multicast) if self._arena is not None else False)
+        return d
+
+    def check_comm_status(self) -> None:
+        """Raise if a peer-memory collective timed out (host-side check, synchronises)."""
+        if self._arena is not None:
+            self._arena.check_status()
