@@ -167,7 +167,7 @@ def test_losses(dtype):
     torch.manual_seed(6)
     p = torch.randn(120, 1000, device=dev()).to(dtype)
     t = torch.randn(120, 1000, device=dev()).to(dtype)
-    pr = p.float().requires_grad_(True)
+    pr = p.float().clone().requires_grad_(True)
     lref = F.mse_loss(pr, t.float()); lref.backward()
     loss, grad = NV.mse_loss_fwd_bwd(p, t)
     tol = 1e-5 if dtype == torch.float32 else 1e-2
@@ -180,13 +180,13 @@ def test_losses(dtype):
     assert abs(s.item() - p.float().sum().item()) < 1e-2 * p.numel() ** 0.5
     assert torch.all(g.float() == 1)
     probs = torch.softmax(torch.randn(120, 1000, device=dev()), -1)
-    pr2 = p.float().requires_grad_(True)
+    pr2 = p.float().clone().requires_grad_(True)
     l2 = F.cross_entropy(pr2, probs); l2.backward()
     l, g = NV.ce_prob_fwd_bwd(p, probs)
     assert abs(l.item() - l2.item()) < 1e-3 * abs(l2.item()) + 1e-4
     assert rel_err(g, pr2.grad) < max(tol, 1e-4)
     labels = torch.randint(0, 1000, (120,), device=dev())
-    pr3 = p.float().requires_grad_(True)
+    pr3 = p.float().clone().requires_grad_(True)
     l3 = F.cross_entropy(pr3, labels); l3.backward()
     l, g = NV.ce_index_fwd_bwd(p, labels)
     assert abs(l.item() - l3.item()) < 1e-3 * abs(l3.item()) + 1e-4
