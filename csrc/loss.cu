@@ -105,7 +105,7 @@ ce_kernel(const T* __restrict__ logits, const float* __restrict__ probs,
     const long long lab = kIndex ? labels[row] : 0;
     for (int c = lane; c < C; c += 32) {
       const float v = ldf(x, c);
-      se += __expf(v - m);
+      se += expf(v - m);
       if (kIndex) {
         if (c == lab) { tsum = 1.f; tx = v; }
       } else {
@@ -117,13 +117,13 @@ ce_kernel(const T* __restrict__ logits, const float* __restrict__ probs,
     se = warp_sum(se);
     tsum = warp_sum(tsum);
     tx = warp_sum(tx);
-    const float lse = m + __logf(se);
+    const float lse = m + logf(se);     // logf(1) == 0 exactly: the C == 1 case stays identically zero
     if (lane == 0) acc += lse * tsum - tx;
     if (grad != nullptr) {
       const float inv = 1.f / se;
       for (int c = lane; c < C; c += 32) {
         const float v = ldf(x, c);
-        const float sm = __expf(v - m) * inv;
+        const float sm = expf(v - m) * inv;
         float t;
         if (kIndex) t = (c == lab) ? 1.f : 0.f;
         else t = probs[(long long)row * C + c];

@@ -37,10 +37,6 @@ class SymmetricArena:
             raise RuntimeError("the peer-memory collectives cover one NVSwitch domain (<= 8 GPUs)")
         nbytes = (int(nbytes) + 4095) // 4096 * 4096
         self.nbytes = nbytes
-        try:
-            symm_mem.enable_symm_mem_for_group(self.group.group_name)
-        except Exception:
-            pass
         self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
         self.sig = symm_mem.empty(SIGNAL_WORDS, dtype=torch.int32, device=device)
         self.buf.zero_()
@@ -90,17 +86,25 @@ def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> st
 class TensorTable:
     """Device-side {ptr, numel} + chunk tables for a fixed list of same-dtype tensors."""
 
-    def __init__(self, numels: Sequence[int], device: torch.device, wire_bf16: bool, tensor_bf16: bool = False) -> None:
+    def __init__(self, numels: Sequence[int], device: torch.device, wire_bf16: bool, tensor_bf16: bool = False,
+                 target_blocks: int = 32) -> None:
         self.device = device
         self.numels = [int(n) for n in numels]
         self.tensor_bf16 = tensor_bf16
         self.wire_bf16 = wire_bf16 or tensor_bf16
+        # chunk size adapts to the payload: mid-size buckets are spread over all CTAs instead of
+        # leaving most of them idle behind a few 64 KB chunks
+        total = sum(self.numels)
+        chunk = CHUNK_ELEMS
+        while chunk > 2048 and total // chunk < target_blocks:
+            chunk //= 2
+        self.chunk_elems = chunk
         rows = []
         off = 0
         for ti, n in enumerate(self.numels):
             s = 0
             while s < n:
-                ln = min(CHUNK_ELEMS, n - s)
+                ln = min(chunk, n - s)
                 rows.append((ti, s, ln, off))
                 off += (ln + 7) // 8 * 8
                 s += ln

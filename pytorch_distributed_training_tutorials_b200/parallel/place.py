@@ -1,0 +1,90 @@
+"""Automatic layer placement by byte budget (the capability behind ``device_map="auto"``).
+
+The reference loads LLaMA-7B with ``device_map="auto"`` and lists where every parameter landed
+(/root/reference/03.model_parallel.ipynb:52-56,114-404): whole decoder layers stay together, are
+assigned to the GPUs in order, the embedding goes with the first layers and the final norm + head
+with the last ones.  ``auto_place`` reproduces that policy for any model that exposes its blocks in
+execution order; ``dispatch`` moves the blocks and installs hooks that move activations.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+from torch import nn
+
+from .comm import _dev
+from .model_parallel import hop
+
+
+def module_bytes(m: nn.Module) -> int:
+    seen, total = set(), 0
+    for t in list(m.parameters()) + list(m.buffers()):
+        if id(t) not in seen:
+            seen.add(id(t))
+            total += t.numel() * t.element_size()
+    return total
+
+
+def execution_blocks(model: nn.Module) -> List[Tuple[str, nn.Module]]:
+    """Top-level children in order; ``ModuleList`` / ``Sequential`` children are expanded one
+    level so that each repeated layer is its own placement unit."""
+    out: List[Tuple[str, nn.Module]] = []
+    for name, child in model.named_children():
+        if isinstance(child, (nn.ModuleList, nn.Sequential)) and len(child) > 1:
+            out.extend((f"{name}.{i}", sub) for i, sub in enumerate(child))
+        else:
+            out.append((name, child))
+    return out
+
+
+def auto_place(model: nn.Module, devices: Sequence, max_memory: Optional[Dict] = None,
+               blocks: Optional[List[Tuple[str, nn.Module]]] = None) -> Dict[str, torch.device]:
+    """Assign consecutive blocks to devices. Each device takes blocks while its budget allows;
+    the last device takes whatever remains. Default budgets: an equal share of the total bytes."""
+    devices = [_dev(d) for d in devices]
+    blocks = blocks if blocks is not None else execution_blocks(model)
+    sizes = [module_bytes(m) for _, m in blocks]
+    total = sum(sizes)
+    if max_memory is None:
+        share = -(-total // len(devices))
+        budgets = [share] * len(devices)
+    else:
+        budgets = [int(max_memory.get(d, max_memory.get(str(d), max_memory.get(d.index, 0)))) for d in devices]
+    placement: Dict[str, torch.device] = {}
+    di, used = 0, 0
+    for (name, _), sz in zip(blocks, sizes):
+        while di < len(devices) - 1 and used + sz > budgets[di] and used > 0:
+            di, used = di + 1, 0
+        placement[name] = devices[di]
+        used += sz
+    return placement
+
+
+def dispatch(model: nn.Module, placement: Dict[str, torch.device]) -> nn.Module:
+    """Move every placed block to its device and make it pull its inputs over on entry."""
+    mods = dict(model.named_modules())
+    for name, dev in placement.items():
+        block = mods[name]
+        block.to(dev)
+
+        def pre_hook(module, args, kwargs, dev=dev):
+            def mv(o):
+                if isinstance(o, torch.Tensor):
+                    return hop(o, dev) if o.is_floating_point() and o.requires_grad else o.to(dev)
+                if isinstance(o, (list, tuple)):
+                    return type(o)(mv(v) for v in o)
+                if isinstance(o, dict):
+                    return {k: mv(v) for k, v in o.items()}
+                return o
+            return mv(args), mv(kwargs)
+
+        block.register_forward_pre_hook(pre_hook, with_kwargs=True)
+    model._b200_placement = placement
+    return model
+
+
+def placement_table(model: nn.Module) -> List[Tuple[int, str, torch.dtype, torch.device]]:
+    """``(index, name, dtype, device)`` per parameter: the listing the reference prints
+    (03.model_parallel.ipynb:409-410)."""
+    return [(i, n, p.dtype, p.device) for i, (n, p) in enumerate(model.named_parameters())]

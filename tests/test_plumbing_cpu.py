@@ -1,0 +1,243 @@
+"""CPU-only unit tests: sampler equality with torch, launch contracts, scatter/gather pytrees,
+checkpoint round trips, placement, pipeline equivalence, bucket assignment."""
+import collections
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+from torch.utils.data import DistributedSampler as TorchSampler
+
+import pytorch_distributed_training_tutorials_b200 as b2
+from pytorch_distributed_training_tutorials_b200.data import DistributedSampler, MyTrainDataset, RandomDataset
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("n", [1, 7, 10, 2048, 2049])
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("shuffle,drop_last,seed", [(True, False, 0), (False, False, 0), (True, True, 5), (False, True, 1)])
+def test_sampler_matches_torch(n, world, shuffle, drop_last, seed):
+    ds = list(range(n))
+    for rank in range(world):
+        a = DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=seed, drop_last=drop_last)
+        b = TorchSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=seed, drop_last=drop_last)
+        for epoch in (0, 1, 7):
+            a.set_epoch(epoch); b.set_epoch(epoch)
+            assert list(a) == list(b)
+            assert len(a) == len(b)
+
+
+def test_sampler_needs_group_or_explicit_rank():
+    with pytest.raises(RuntimeError):
+        DistributedSampler(list(range(4)))
+    with pytest.raises(ValueError):
+        DistributedSampler(list(range(4)), num_replicas=2, rank=2)
+
+
+def test_steps_per_epoch_match_reference_banner():
+    # 2048 samples, per-rank batch 32: 16 steps on 4 ranks, 64 on one (02.ddp_toy_example.ipynb:231,268)
+    ds = MyTrainDataset(2048)
+    for world, steps in ((4, 16), (1, 64), (2, 32), (8, 8)):
+        s = DistributedSampler(ds, num_replicas=world, rank=0)
+        dl = torch.utils.data.DataLoader(ds, batch_size=32, sampler=s)
+        assert len(dl) == steps
+    x, y = ds[0]
+    assert x.shape == (20,) and y.shape == (1,)
+    assert len(RandomDataset(32, 1024)) == 1024 and RandomDataset(32, 1024)[0].shape == (32,)
+
+
+def test_scatter_gather_pytrees():
+    from pytorch_distributed_training_tutorials_b200.parallel.data_parallel import gather, scatter, scatter_kwargs
+    devs = ["cpu"] * 4
+    x = torch.arange(32 * 3).float().view(32, 3)
+    chunks = scatter(x, devs)
+    assert [c.shape[0] for c in chunks] == [8, 8, 8, 8]
+    assert [c.shape[0] for c in scatter(torch.zeros(10, 2), devs)] == [3, 3, 3, 1]
+    assert len(scatter(torch.zeros(2, 2), devs)) == 2                  # fewer chunks than devices
+    NT = collections.namedtuple("NT", ["a", "b"])
+    tree = (x, [x, {"k": x}], NT(x, 5), "s")
+    parts = scatter(tree, devs)
+    assert len(parts) == 4 and parts[1][0].shape == (8, 3) and parts[2][1][1]["k"].shape == (8, 3)
+    assert isinstance(parts[0][2], NT) and parts[3][2].b == 5 and parts[0][3] == "s"
+    ins, kws = scatter_kwargs((x,), {"m": x}, devs)
+    assert len(ins) == len(kws) == 4 and kws[2]["m"].shape == (8, 3)
+    ins, kws = scatter_kwargs((), {"m": x}, devs)
+    assert ins == ((), (), (), ())
+    outs = [{"o": c * 2, "n": None, "t": (c, c)} for c in chunks]
+    g = gather(outs, "cpu")
+    assert torch.equal(g["o"], x * 2) and g["n"] is None and torch.equal(g["t"][1], x)
+    with pytest.warns(UserWarning):
+        v = gather([torch.tensor(1.0), torch.tensor(2.0)], "cpu")
+    assert v.tolist() == [1.0, 2.0]
+
+
+def test_data_parallel_virtual_devices_matches_chunked_reference(capsys):
+    import copy
+    from pytorch_distributed_training_tutorials_b200.models.toy import SampleModel
+    from pytorch_distributed_training_tutorials_b200.parallel.data_parallel import DataParallel
+    torch.manual_seed(0)
+    m = SampleModel(32, 2)
+    ref = copy.deepcopy(m); ref.verbose = False
+    dp = DataParallel(m, device_ids=["cpu"] * 4)
+    x = torch.randn(32, 32)
+    out = dp(x)
+    printed = capsys.readouterr().out
+    assert printed.count("In Model: input size torch.Size([8, 32]) output size torch.Size([8, 2])") == 4
+    assert out.shape == (32, 2)
+    out.sum().backward()
+    ref(x).sum().backward()
+    for p, q in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-5)
+    assert list(dp.state_dict().keys()) == ["module.fc.weight", "module.fc.bias"]
+    s, o = dp.forward_sum(x)
+    assert torch.allclose(s, ref(x).sum(), atol=1e-4) and o.shape == (32, 2)
+    # errors inside a replica surface in the caller with the replica index
+    class Boom(torch.nn.Module):
+        def forward(self, x):
+            raise ValueError("bad replica")
+    with pytest.raises(ValueError, match="replica"):
+        DataParallel(Boom(), device_ids=["cpu", "cpu"])(x)
+
+
+def test_checkpoint_roundtrip_with_plain_torch(tmp_path):
+    from pytorch_distributed_training_tutorials_b200.checkpoint import load_checkpoint, save_checkpoint
+    from pytorch_distributed_training_tutorials_b200.parallel.data_parallel import DataParallel
+    m = torch.nn.Sequential(torch.nn.Linear(4, 3), torch.nn.BatchNorm1d(3))
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    m(torch.randn(5, 4)).sum().backward(); opt.step()
+    wrapped = DataParallel(m, device_ids=["cpu", "cpu"])
+    path = str(tmp_path / "ckpt.pt")
+    assert save_checkpoint(wrapped, opt, epoch=4, path=path, extra={"note": "x"}) == path
+    blob = torch.load(path, weights_only=False)
+    assert not any(k.startswith("module.") for k in blob["model"])
+    plain = torch.nn.Sequential(torch.nn.Linear(4, 3), torch.nn.BatchNorm1d(3))
+    plain.load_state_dict(blob["model"])                              # plain torch reads our file
+    m2 = torch.nn.Sequential(torch.nn.Linear(4, 3), torch.nn.BatchNorm1d(3))
+    o2 = torch.optim.Adam(m2.parameters(), lr=1e-3)
+    info = load_checkpoint(path, DataParallel(m2, device_ids=["cpu"]), o2)
+    assert info["epoch"] == 4 and info["extra"] == {"note": "x"} and not info["missing"]
+    assert torch.equal(m2[0].weight, m[0].weight)
+    assert o2.state_dict()["state"][0]["exp_avg"].equal(opt.state_dict()["state"][0]["exp_avg"])
+    # a file written by plain torch from a wrapped model (module. prefix) loads too
+    torch.save({"module." + k: v for k, v in m.state_dict().items()}, path)
+    assert load_checkpoint(path, m2)["missing"] == []
+
+
+def test_checkpoint_dedups_aliased_registration(tmp_path):
+    from pytorch_distributed_training_tutorials_b200.checkpoint import load_checkpoint, model_state
+
+    class Twice(torch.nn.Module):      # the reference's split ResNet registers layers twice
+        def __init__(self):
+            super().__init__()
+            self.layer1 = torch.nn.Linear(3, 3)
+            self.seq1 = torch.nn.Sequential(self.layer1)
+    t = Twice()
+    assert set(t.state_dict()) == {"layer1.weight", "layer1.bias", "seq1.0.weight", "seq1.0.bias"}
+    sd = model_state(t)
+    assert set(sd) == {"layer1.weight", "layer1.bias"}
+    torch.save(sd, tmp_path / "a.pt")
+    t2 = Twice()
+    assert load_checkpoint(str(tmp_path / "a.pt"), t2)["missing"] == []
+    assert torch.equal(t2.seq1[0].weight, t.layer1.weight)
+
+
+def test_auto_place_reproduces_reference_listing():
+    from pytorch_distributed_training_tutorials_b200.models.llama_like import LlamaLikeForCausalLM
+    from pytorch_distributed_training_tutorials_b200.parallel.place import auto_place, module_bytes, placement_table
+    m = LlamaLikeForCausalLM(vocab=64, dim=16, layers=32, heads=2, hidden=32)
+    assert len(list(m.parameters())) == 291                           # 03.model_parallel.ipynb:114-404
+    blocks = m.placement_blocks()
+    layer = module_bytes(m.model.layers[0]); emb = module_bytes(m.model.embed_tokens)
+    devs = [torch.device("cuda", i) for i in range(4)]                 # placement is pure bookkeeping
+    budgets = {devs[0]: emb + 6 * layer, devs[1]: 8 * layer, devs[2]: 8 * layer, devs[3]: 10 ** 12}
+    pl = auto_place(m, devs, max_memory=budgets, blocks=blocks)
+    per_dev = collections.Counter()
+    for name, dev in pl.items():
+        sub = dict(m.named_modules())[name]
+        per_dev[dev.index] += len(list(sub.parameters()))
+    assert [per_dev[i] for i in range(4)] == [55, 72, 72, 92]
+    bal = auto_place(m, devs, blocks=blocks)                           # balanced default keeps order
+    idx = [bal[n].index for n, _ in blocks]
+    assert idx == sorted(idx) and set(idx) == {0, 1, 2, 3}
+    assert len(placement_table(m)) == 291
+
+
+def test_staged_and_pipelined_equal_plain_module():
+    from pytorch_distributed_training_tutorials_b200.parallel.model_parallel import Pipeline, StagedModule, split_sequential, model_size
+    torch.manual_seed(0)
+    seq = torch.nn.Sequential(torch.nn.Linear(6, 8), torch.nn.ReLU(), torch.nn.Linear(8, 8), torch.nn.ReLU(), torch.nn.Linear(8, 2))
+    stages = split_sequential(seq, [2, 4])
+    assert len(stages) == 3
+    x = torch.randn(10, 6)
+    ref = seq(x)
+    st = StagedModule(stages, ["cpu"] * 3)
+    assert torch.allclose(st(x), ref)
+    pp = Pipeline(stages, ["cpu"] * 3, split_size=3)
+    out = pp(x)
+    assert torch.allclose(out, ref, atol=1e-6)
+    out.sum().backward()
+    g = [p.grad.clone() for p in seq.parameters()]
+    seq.zero_grad(); seq(x).sum().backward()
+    assert all(torch.allclose(a, p.grad, atol=1e-5) for a, p in zip(g, seq.parameters()))
+    assert model_size(st) == model_size(seq)
+
+
+def test_split_resnet_has_reference_param_count():
+    from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_training_tutorials_b200.parallel.model_parallel import model_size
+    assert model_size(resnet50(num_classes=1000)) == 25557032          # 03.model_parallel.ipynb:857,888
+
+
+def test_bucket_assignment_matches_torch_resnet50():
+    import torchvision
+    from pytorch_distributed_training_tutorials_b200.parallel._native_reducer import load
+    R = load()
+    ps = list(torchvision.models.resnet50().parameters())
+    rev = list(reversed(ps)); idx = list(reversed(range(len(ps))))
+    mine, _ = R.assign_buckets(rev, [1 << 20, 25 << 20], idx)
+    ref, _ = dist._compute_bucket_assignment_by_size(rev, [1 << 20, 25 << 20], [False] * len(ps), idx)
+    assert mine == ref and len(mine) == 5
+    a, _ = R.assign_buckets(ps, [2 ** 62])
+    assert a == [list(range(len(ps)))]
+
+
+def test_run_launcher_env_contract(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(
+        "import os, json\n"
+        "keys = ['LOCAL_RANK','RANK','GROUP_RANK','ROLE_RANK','LOCAL_WORLD_SIZE','WORLD_SIZE','MASTER_ADDR',"
+        "'MASTER_PORT','TORCHELASTIC_RESTART_COUNT','TORCHELASTIC_MAX_RESTARTS','TORCHELASTIC_RUN_ID','OMP_NUM_THREADS']\n"
+        f"open(r'{tmp_path}' + '/env' + os.environ['RANK'] + '.json','w').write(json.dumps({{k: os.environ.get(k) for k in keys}}))\n")
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    env.pop("OMP_NUM_THREADS", None)
+    r = subprocess.run([sys.executable, "-m", "pytorch_distributed_training_tutorials_b200.run", "--standalone",
+                        "--nproc-per-node", "3", str(script)], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert "Setting OMP_NUM_THREADS" in r.stderr
+    import json
+    envs = [json.load(open(tmp_path / f"env{i}.json")) for i in range(3)]
+    assert [e["LOCAL_RANK"] for e in envs] == ["0", "1", "2"] and all(e["WORLD_SIZE"] == "3" for e in envs)
+    assert all(e["MASTER_ADDR"] == "127.0.0.1" and e["OMP_NUM_THREADS"] == "1" for e in envs)
+    assert len({e["MASTER_PORT"] for e in envs}) == 1
+    # default is ONE worker, like torchrun without --nproc-per-node (02.ddp_toy_example.ipynb:268)
+    for f in tmp_path.glob("env*.json"):
+        f.unlink()
+    r = subprocess.run([sys.executable, "-m", "pytorch_distributed_training_tutorials_b200.run", "--standalone",
+                        str(script)], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and sorted(p.name for p in tmp_path.glob("env*.json")) == ["env0.json"]
+
+
+def test_run_launcher_failure_and_restart(tmp_path):
+    script = tmp_path / "f.py"
+    script.write_text("import os, sys, time\n"
+                      "if os.environ['RANK'] == '1' and os.environ['TORCHELASTIC_RESTART_COUNT'] == '0': sys.exit(3)\n"
+                      "time.sleep(0.2)\n")
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    base = [sys.executable, "-m", "pytorch_distributed_training_tutorials_b200.run", "--standalone", "--nproc-per-node", "2"]
+    r = subprocess.run(base + [str(script)], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3 and "failed with exit code 3" in r.stderr
+    r = subprocess.run(base + ["--max-restarts", "1", str(script)], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "restarting worker group (1/1)" in r.stderr
