@@ -117,19 +117,23 @@ ce_kernel(const T* __restrict__ logits, const float* __restrict__ probs,
     se = warp_sum(se);
     tsum = warp_sum(tsum);
     tx = warp_sum(tx);
-    const float lse = m + logf(se);     // logf(1) == 0 exactly: the C == 1 case stays identically zero
-    if (lane == 0) acc += lse * tsum - tx;
-    if (grad != nullptr) {
-      const float inv = 1.f / se;
-      for (int c = lane; c < C; c += 32) {
-        const float v = ldf(x, c);
+    const float lse = m + logf(se);
+    // loss_row = sum_c t_c * (lse - x_c), accumulated term by term: with a single class the term
+    // is t * 0, so the reference's degenerate case (ddp_gpus.py:37) is exactly zero.
+    const float inv = 1.f / se;
+    float row_loss = 0.f;
+    for (int c = lane; c < C; c += 32) {
+      const float v = ldf(x, c);
+      float t;
+      if (kIndex) t = (c == lab) ? 1.f : 0.f;
+      else t = probs[(long long)row * C + c];
+      row_loss += t * (lse - v);
+      if (grad != nullptr) {
         const float sm = expf(v - m) * inv;
-        float t;
-        if (kIndex) t = (c == lab) ? 1.f : 0.f;
-        else t = probs[(long long)row * C + c];
         stf(grad + (long long)row * C, c, (sm * tsum - t) * gs);
       }
     }
+    acc += row_loss;
   }
   acc = block_sum(acc, red);
   finish_scalar(acc, sc, loss, 1.f / (float)B, red);

@@ -23,25 +23,37 @@ def test_resnet50_matches_torchvision():
     y = torch.randint(0, 1000, (16,), device=dev)
     out_ref = ref(x)
     F.cross_entropy(out_ref, y).backward()
+    # yardstick: what bf16 compute costs the library stack itself on this batch: torchvision under
+    # autocast vs the fp32 run above (at random init the gradients below the last block are
+    # dominated by bf16 rounding for BOTH stacks; bench/diag_resnet_grads.py prints the table)
+    import copy
+    amp = copy.deepcopy(ref)
+    amp.zero_grad()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out_amp = amp(x)
+        F.cross_entropy(out_amp, y).backward()
+    amp_err = rel(out_amp.float(), out_ref)
     out = mine(x)
     assert out.shape == (16, 1000) and out.dtype == torch.float32
     from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
     loss = Fn.cross_entropy(out, y)
     loss.backward()
-    assert rel(out, out_ref) < 5e-2
+    assert rel(out, out_ref) < 2.5 * amp_err + 2e-2, (rel(out, out_ref), amp_err)
+    assert F.cosine_similarity(out.flatten(), out_ref.flatten(), dim=0).item() > 0.97
     # BN running statistics follow the same update rule
     assert rel(mine.bn1.running_var, ref.bn1.running_var) < 2e-2
     assert rel(mine.layer4[2].bn3.running_mean, ref.layer4[2].bn3.running_mean) < 5e-2
-    # gradients: bf16 activations through 50 layers; compare direction and scale
-    pairs = [(mine.fc.weight.grad, ref.fc.weight.grad),
-             (mine.layer4[2].conv3.weight.grad.permute(0, 3, 1, 2), ref.layer4[2].conv3.weight.grad),
-             (mine.layer3[0].conv2.weight.grad.permute(0, 3, 1, 2), ref.layer3[0].conv2.weight.grad),
-             (mine.layer1[0].conv1.weight.grad.permute(0, 3, 1, 2), ref.layer1[0].conv1.weight.grad),
-             (mine.conv1.weight.grad.permute(0, 3, 1, 2), ref.conv1.weight.grad),
-             (mine.bn1.weight.grad, ref.bn1.weight.grad)]
-    for i, (a, b) in enumerate(pairs):
-        cos = F.cosine_similarity(a.flatten().float(), b.flatten().float(), dim=0).item()
-        assert cos > 0.95, (i, cos, rel(a, b))
+    # gradients: agree with fp32 at least as well as the library's own bf16 path does
+    pm, pr, pa = dict(mine.named_parameters()), dict(ref.named_parameters()), dict(amp.named_parameters())
+    for n in ["fc.weight", "fc.bias", "layer4.2.bn3.weight", "layer4.2.conv3.weight", "layer3.0.conv2.weight",
+              "layer1.0.conv1.weight", "conv1.weight"]:
+        g = pm[n].grad.permute(0, 3, 1, 2) if pm[n].grad.dim() == 4 else pm[n].grad
+        a_, b_, c_ = g.flatten().float(), pr[n].grad.flatten().float(), pa[n].grad.flatten().float()
+        cos_mine = F.cosine_similarity(a_, b_, dim=0).item()
+        cos_amp = F.cosine_similarity(c_, b_, dim=0).item()
+        assert cos_mine > cos_amp - 0.08, (n, cos_mine, cos_amp)
+        assert 0.8 < (a_.norm() / b_.norm()).item() < 1.25, n
+    assert F.cosine_similarity(pm["fc.weight"].grad.flatten(), pr["fc.weight"].grad.flatten(), dim=0).item() > 0.98
 
 
 def test_resnet50_trains_and_checkpoint_roundtrip(tmp_path):
@@ -51,18 +63,29 @@ def test_resnet50_trains_and_checkpoint_roundtrip(tmp_path):
     from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
     torch.manual_seed(1)
     dev = torch.device("cuda:0")
-    m = resnet50(num_classes=10).to(dev)
-    opt = FusedSGD(m.parameters(), lr=0.05)
-    x = torch.randn(32, 3, 64, 64, device=dev)
-    y = torch.randint(0, 10, (32,), device=dev)
-    losses = []
-    for _ in range(8):
+    ref = torchvision.models.resnet50(num_classes=1000).to(dev).train()
+    m = resnet50(num_classes=1000).to(dev).train()
+    m.load_state_dict(ref.state_dict())
+    opt = FusedSGD(m.parameters(), lr=0.01)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.01)
+    x = torch.randn(64, 3, 224, 224, device=dev)
+    y = torch.randint(0, 1000, (64,), device=dev)
+    losses, rlosses = [], []
+    for _ in range(6):
         opt.zero_grad()
         loss = Fn.cross_entropy(m(x), y)
         loss.backward()
         opt.step()
         losses.append(loss.item())
+        ropt.zero_grad()
+        rl = F.cross_entropy(ref(x), y)
+        rl.backward()
+        ropt.step()
+        rlosses.append(rl.item())
     assert losses[-1] < losses[0], losses          # it overfits one batch
+    # same trajectory as the fp32 torchvision model trained with torch.optim.SGD
+    for a_, b_ in zip(losses, rlosses):
+        assert abs(a_ - b_) < 0.02 * abs(b_), (losses, rlosses)
     torch.save(m.state_dict(), tmp_path / "m.pt")
-    tv = torchvision.models.resnet50(num_classes=10)
+    tv = torchvision.models.resnet50(num_classes=1000)
     tv.load_state_dict(torch.load(tmp_path / "m.pt"))  # our checkpoints load into plain torchvision
