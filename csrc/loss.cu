@@ -214,3 +214,109 @@ extern "C" int b200dt_ce_index_loss(const void* logits, const long long* labels,
                                               loss, B, C, grad_scale, (LossScratch*)scratch);
   return (int)cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------
+// MSE loss for callers that must not allocate.
+//
+// Some users of this library run where cudaMalloc is off limits: a training loop whose memory
+// was carved up once at start-up and handed out by its own arena, a plugin living inside
+// another runtime that owns the device heap, or code running while allocation is forbidden
+// (for example inside a region that has been frozen for replay).  b200dt_mse_loss() needs a
+// scratch buffer from its caller; the variant below keeps that scratch inside the library image
+// instead, in a fixed array in device global memory.  Every GPU that loads the library pays for
+// the array (B200DT_MSE_STATIC_SCRATCH_BYTES, about 1 KB) until the process exits, which is why it
+// is kept small and why the entry point only accepts up to B200DT_MSE_STATIC_MAX_ELEMS elements:
+// one partial-sum slot per 4096-element tile, 256 slots.
+namespace b200 {
+
+constexpr int kStaticTile = 4096;                 // elements reduced by one CTA
+constexpr int kStaticSlots = 256;                 // partial sums held in the static scratch
+struct StaticLossScratch {
+  float partial[kStaticSlots];
+  unsigned int ticket;
+  unsigned int pad[3];
+};
+static_assert(sizeof(StaticLossScratch) == B200DT_MSE_STATIC_SCRATCH_BYTES, "header and kernel disagree");
+static_assert((long long)kStaticTile * kStaticSlots == B200DT_MSE_STATIC_MAX_ELEMS, "header and kernel disagree");
+
+// The scratch itself.  In host code this name is only a handle for the runtime's symbol table,
+// not an address the GPU understands; the address is looked up per device further down.
+static __device__ __align__(256) unsigned char g_mse_static_scratch[sizeof(StaticLossScratch)];
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+mse_static_kernel(const T* __restrict__ pred, const T* __restrict__ target, T* __restrict__ grad,
+                  float* loss, long long n, float gscale, StaticLossScratch* sc) {
+  __shared__ float red[32];
+  __shared__ bool is_last;
+  float acc = 0.f;
+  const float gs = 2.f * gscale / (float)n;
+  const long long begin = (long long)blockIdx.x * kStaticTile;
+  const long long end = begin + kStaticTile < n ? begin + kStaticTile : n;
+  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
+    const float d = ldf(pred, i) - ldf(target, i);
+    acc += d * d;
+    if (grad != nullptr) stf(grad, i, d * gs);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) {
+    sc->partial[blockIdx.x] = acc;
+    __threadfence();
+    is_last = (atomicAdd(&sc->ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    float s = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x)
+      s += *reinterpret_cast<volatile float*>(&sc->partial[i]);
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) *loss = s / (float)n;
+  }
+}
+
+constexpr int kMaxDevices = 64;
+static void* g_mse_static_ptr[kMaxDevices] = {nullptr};
+
+// Device address of the scratch on the CURRENT device, resolved once per device.
+static int mse_static_scratch_for_current_device(StaticLossScratch** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return -8;
+  void* p = __atomic_load_n(&g_mse_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(&p, g_mse_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return -8;
+    // two threads racing here resolve the same address; either store is fine
+    __atomic_store_n(&g_mse_static_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = reinterpret_cast<StaticLossScratch*>(p);
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" int b200dt_mse_loss_static(const void* pred, const void* target, void* grad, float* loss,
+                                      long long n, float grad_scale, int is_bf16, void* stream) {
+  if (n <= 0 || pred == nullptr || target == nullptr || loss == nullptr) return -3;
+  if (n > B200DT_MSE_STATIC_MAX_ELEMS) return -9;      // more tiles than partial-sum slots
+  StaticLossScratch* sc = nullptr;
+  int rc = mse_static_scratch_for_current_device(&sc);
+  if (rc != 0) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array still holds whatever the previous call left; only the ticket has to start at zero
+  // (every partial slot that is read is written first by this launch).
+  cudaError_t e = cudaMemsetAsync(&sc->ticket, 0, sizeof(unsigned int), st);
+  if (e != cudaSuccess) return (int)e;
+  const int grid = (int)((n + kStaticTile - 1) / kStaticTile);
+  if (is_bf16)
+    mse_static_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
+        (const __nv_bfloat16*)pred, (const __nv_bfloat16*)target, (__nv_bfloat16*)grad, loss, n,
+        grad_scale, sc);
+  else
+    mse_static_kernel<float><<<grid, 256, 0, st>>>((const float*)pred, (const float*)target,
+                                                   (float*)grad, loss, n, grad_scale, sc);
+  return (int)cudaGetLastError();
+}

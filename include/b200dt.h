@@ -102,6 +102,25 @@ int b200dt_ce_prob_loss(const void* logits, const float* probs, void* grad, floa
 int b200dt_ce_index_loss(const void* logits, const long long* labels, void* grad, float* loss,
                          int B, int C, float grad_scale, int is_bf16, void* scratch, void* stream);
 
+/* MSE loss for callers that cannot allocate device memory (no counterpart in the reference, which
+ * never manages memory itself). Same result as b200dt_mse_loss, but the reduction scratch is a
+ * fixed B200DT_MSE_STATIC_SCRATCH_BYTES array inside the library's device image, so the call does
+ * no cudaMalloc / cudaFree and needs no scratch argument; inputs and outputs are still the
+ * caller's. Meant for hosts with a pre-carved memory arena, plugins inside a runtime that owns
+ * the heap, or phases where allocating is forbidden.
+ *  - n must be <= B200DT_MSE_STATIC_MAX_ELEMS (one partial-sum slot per 4096 elements, 256
+ *    slots); larger inputs return -9 and launch nothing.
+ *  - The first call on each device looks up the device address of the array
+ *    (cudaGetSymbolAddress, with that device current); make that first call before starting any
+ *    stream capture.
+ *  - All calls on a device share the one array: two calls whose kernels may overlap on the GPU
+ *    (different streams without ordering) race on it. Order them, or use b200dt_mse_loss with
+ *    separate scratch buffers. The array lives on every GPU that loads the library until exit. */
+#define B200DT_MSE_STATIC_SCRATCH_BYTES 1040
+#define B200DT_MSE_STATIC_MAX_ELEMS 1048576LL
+int b200dt_mse_loss_static(const void* pred, const void* target, void* grad, float* loss,
+                           long long n, float grad_scale, int is_bf16, void* stream);
+
 /* ---------------------------------------------------------------- optimizers (csrc/optim.cu)
  * Replaces torch.optim.SGD (ddp_gpus.py:82) / Adam (01.data_parallel.ipynb:287) foreach kernels.
  * meta: device int64 [n_tensors, 8] = {param, grad, shadow_bf16|0, numel, exp_avg|0, exp_avg_sq|0,
