@@ -13,6 +13,7 @@
 namespace b200 {
 
 constexpr int kBnThreads = 256;
+constexpr int kUnroll = 4;       // independent 16-byte loads in flight per thread and stream
 
 struct Slab {
   int cols_per_block;   // vector (8-channel) columns handled by one CTA
@@ -65,8 +66,21 @@ bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
   if (col < cv) {
-    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
-         r += (long long)gridDim.y * rowlanes) {
+    const long long stride = (long long)gridDim.y * rowlanes;
+    long long r = (long long)blockIdx.y * rowlanes + ty;
+    for (; r + (kUnroll - 1) * stride < rows; r += kUnroll * stride) {
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) v[u] = ld_nc_v4(x + (r + u * stride) * cv + col);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        float f[8];
+        unpack8(v[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] += f[j] * f[j]; }
+      }
+    }
+    for (; r < rows; r += stride) {
       float f[8];
       unpack8(ld_nc_v4(x + r * cv + col), f);
 #pragma unroll
@@ -121,23 +135,38 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
       }
     }
   }
-  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
-       r += (long long)gridDim.y * rowlanes) {
-    float f[8];
-    unpack8(ld_nc_v4(x + r * cv + col), f);
+  const long long stride = (long long)gridDim.y * rowlanes;
+  long long r = (long long)blockIdx.y * rowlanes + ty;
+  for (; r < rows; r += kUnroll * stride) {
+    uint4 vx[kUnroll], vr[kUnroll];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
-    if (res != nullptr) {
-      float g[8];
-      unpack8(ld_nc_v4(res + r * cv + col), g);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += g[j];
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long rr = r + u * stride;
+      if (rr < rows) {
+        vx[u] = ld_nc_v4(x + rr * cv + col);
+        if (res != nullptr) vr[u] = ld_nc_v4(res + rr * cv + col);
+      }
     }
-    if (relu) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long rr = r + u * stride;
+      if (rr >= rows) break;
+      float f[8];
+      unpack8(vx[u], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
+      if (res != nullptr) {
+        float g[8];
+        unpack8(vr[u], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] += g[j];
+      }
+      if (relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      y[rr * cv + col] = pack8(f);
     }
-    y[r * cv + col] = pack8(f);
   }
 }
 
@@ -161,22 +190,37 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
     invstd[j] = save_invstd[c];
   }
   if (col < cv) {
-    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
-         r += (long long)gridDim.y * rowlanes) {
-      float g[8], xv[8];
-      unpack8(ld_nc_v4(dy + r * cv + col), g);
-      unpack8(ld_nc_v4(x + r * cv + col), xv);
-      if (relu) {
-        float yv[8];
-        unpack8(ld_nc_v4(y + r * cv + col), yv);
+    const long long stride = (long long)gridDim.y * rowlanes;
+    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnroll * stride) {
+      uint4 vg[kUnroll], vx[kUnroll], vy[kUnroll];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long rr = r + u * stride;
+        if (rr < rows) {
+          vg[u] = ld_nc_v4(dy + rr * cv + col);
+          vx[u] = ld_nc_v4(x + rr * cv + col);
+          if (relu) vy[u] = ld_nc_v4(y + rr * cv + col);
+        }
       }
-      if (dres != nullptr) dres[r * cv + col] = pack8(g);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        acc[0][j] += g[j];
-        acc[1][j] += g[j] * (xv[j] - mean[j]) * invstd[j];
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long rr = r + u * stride;
+        if (rr >= rows) break;
+        float g[8], xv[8];
+        unpack8(vg[u], g);
+        unpack8(vx[u], xv);
+        if (relu) {
+          float yv[8];
+          unpack8(vy[u], yv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        }
+        if (dres != nullptr) dres[rr * cv + col] = pack8(g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc[0][j] += g[j];
+          acc[1][j] += g[j] * (xv[j] - mean[j]) * invstd[j];
+        }
       }
     }
   }
@@ -215,23 +259,38 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
       if (dgamma != nullptr) dgamma[c] = sums[C + c];
     }
   }
-  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows;
-       r += (long long)gridDim.y * rowlanes) {
-    float g[8], xv[8];
-    unpack8(ld_nc_v4(dy + r * cv + col), g);
-    unpack8(ld_nc_v4(x + r * cv + col), xv);
-    if (relu) {
-      float yv[8];
-      unpack8(ld_nc_v4(y + r * cv + col), yv);
+  const long long stride = (long long)gridDim.y * rowlanes;
+  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnroll * stride) {
+    uint4 vg[kUnroll], vx[kUnroll], vy[kUnroll];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long rr = r + u * stride;
+      if (rr < rows) {
+        vg[u] = ld_nc_v4(dy + rr * cv + col);
+        vx[u] = ld_nc_v4(x + rr * cv + col);
+        if (relu) vy[u] = ld_nc_v4(y + rr * cv + col);
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float xhat = (xv[j] - mean[j]) * invstd[j];
-      g[j] = scale[j] * (g[j] - mg[j] - xhat * mgx[j]);
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long rr = r + u * stride;
+      if (rr >= rows) break;
+      float g[8], xv[8];
+      unpack8(vg[u], g);
+      unpack8(vx[u], xv);
+      if (relu) {
+        float yv[8];
+        unpack8(vy[u], yv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xhat = (xv[j] - mean[j]) * invstd[j];
+        g[j] = scale[j] * (g[j] - mg[j] - xhat * mgx[j]);
+      }
+      dx[rr * cv + col] = pack8(g);
     }
-    dx[r * cv + col] = pack8(g);
   }
 }
 

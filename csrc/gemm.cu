@@ -15,6 +15,7 @@
 // Replaces what the reference reaches through cuBLAS / cuDNN: nn.Linear
 // (/root/reference/ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)
 // and the torchvision ResNet-50 convolutions (03.model_parallel.ipynb:807-833).
+#include <stdlib.h>
 #include "ptx.cuh"
 #include "common.cuh"
 #include "../include/b200dt.h"
@@ -23,9 +24,10 @@ namespace b200 {
 
 constexpr int kBM = 128;          // UMMA M (cta_group::1)
 constexpr int kBK = 64;           // K elements per stage (one 128-byte swizzle row)
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;          // 2 control warps + 8 epilogue warps
 constexpr int kMaxTaps = 9;
 constexpr int kMaxMaps = 4;
+constexpr int kStageOutBytes = 128 * 128;   // 8 epilogue warps x (32 rows x 128 B); x2 = budget kept for staging
 
 struct Tap {
   int8_t map, dw, dh, pad;
@@ -50,6 +52,9 @@ struct GemmParams {
   int n_valid;              // valid output columns
   int m_valid;              // WGRAD: valid output rows (Cout)
   int out_fp32, relu, atomic;
+  int qbox[3];              // per-warp store sub-box (w, h, n): a quarter (32 rows) of the tile
+  int qoff[4][3];           // origin of quarter q inside the tile box (w, h, n)
+  int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   const float* bias;
 };
 
@@ -109,7 +114,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                const __grid_constant__ CUtensorMap mapA2, const __grid_constant__ CUtensorMap mapA3,
                const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
                const __grid_constant__ CUtensorMap mapB2, const __grid_constant__ CUtensorMap mapB3,
-               const __grid_constant__ GemmParams p) {
+               const __grid_constant__ CUtensorMap mapC, const __grid_constant__ GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms.
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -117,7 +122,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
   const int a_stage_bytes = kBM * kBK * 2;            // 16 KB
   const int b_stage_bytes = p.BN * kBK * 2;           // 8..32 KB
   const int stage_bytes = a_stage_bytes + b_stage_bytes;
-  Barriers* bars = reinterpret_cast<Barriers*>(smem + p.stages * stage_bytes);
+  uint8_t* stage_out = smem + p.stages * stage_bytes;          // 2 x 16 KB epilogue staging
+  Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -126,13 +132,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&mapA0);
     tma_prefetch_desc(&mapB0);
+    if (p.tma_store) tma_prefetch_desc(&mapC);
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&bars->full[i], 1);
       mbar_init(&bars->empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->tmem_full[i], 1);
-      mbar_init(&bars->tmem_empty[i], 128);
+      mbar_init(&bars->tmem_empty[i], 8);        // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -238,60 +245,180 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue
+    // ------------------------------------------------------------ epilogue (warps 2..9)
+    // Two warps per TMEM lane quarter; each warp is an independent pipeline over its column
+    // slabs: tcgen05.ld -> (bias / ReLU) -> swizzled 4 KB smem tile -> its own TMA store of a
+    // 32-row sub-box.  No CTA-wide barrier is needed anywhere in the epilogue.
     const int q = warp & 3;                // TMEM lane quarter this warp may touch
+    const int pi = (warp - 2) >> 2;        // which of the two warps of the quarter
     const int row = q * 32 + lane;
+    uint8_t* buf = stage_out + (warp - 2) * 4096;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int n_blk = t % p.tiles_n;
       const int m_blk = (t / p.tiles_n) % p.tiles_m;
-      bool row_ok;
-      long long row_off;
-      int col_base;
+      const int col_base = n_blk * p.BN;   // WGRAD: taps are consecutive, tap * Cin + ct * BN
+      int tw = 0, th = 0, tn = 0;
       if (p.kind == 0) {
-        const int tw = m_blk % p.tiles_w;
-        const int th = (m_blk / p.tiles_w) % p.tiles_h;
-        const int tn = m_blk / (p.tiles_w * p.tiles_h);
-        const int dw = row % p.bw;
-        const int dh = (row / p.bw) % p.bh;
-        const int dn = row / (p.bw * p.bh);
-        const int w = tw * p.bw + dw, h = th * p.bh + dh, n = tn * p.bn + dn;
-        row_ok = (w < p.W) && (h < p.H) && (n < p.NB);
-        row_off = n * p.sN + h * p.sH + w * p.sW;
-        col_base = n_blk * p.BN;
-      } else {
-        const int r = m_blk * kBM + row;
-        row_ok = r < p.m_valid;
-        row_off = static_cast<long long>(r) * p.sW;
-        col_base = n_blk * p.BN;     // taps are laid out consecutively: tap * Cin + ct * BN
+        tw = m_blk % p.tiles_w;
+        th = (m_blk / p.tiles_w) % p.tiles_h;
+        tn = m_blk / (p.tiles_w * p.tiles_h);
       }
       mbar_wait(&bars->tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * p.BN;
-      for (int c = 0; c < p.BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(taddr + c * 32, v);
-        tmem_ld_wait();
-        float f[32];
-        const int col0 = col_base + c * 32;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < p.n_valid) f[j] += __ldg(p.bias + col0 + j);
+      if (p.tma_store) {
+        const int cols_per_slab = p.out_fp32 ? 32 : 64;
+        const int nslabs = p.BN / cols_per_slab;
+        int c1, c2, c3;                    // origin of this warp's 32-row sub-box in the output map
+        if (p.kind == 0) {
+          c1 = tw * p.bw + p.qoff[q][0]; c2 = th * p.bh + p.qoff[q][1]; c3 = tn * p.bn + p.qoff[q][2];
+        } else {
+          c1 = m_blk * kBM + q * 32; c2 = 0; c3 = 0;
         }
-        if (p.relu) {
+        uint8_t* my_row = buf + lane * 128;
+        const int sw = lane & 7;
+        const bool plain = (p.bias == nullptr) && !p.relu;       // uniform across the CTA
+        for (int sl = pi; sl < nslabs; sl += 2) {
+          const int col0 = col_base + sl * cols_per_slab;
+          if (col0 >= p.n_valid) break;    // uniform: whole slab is outside the tensor
+          const bool full = (col0 + cols_per_slab <= p.n_valid);
+          if (p.out_fp32) {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr + sl * 32, v);
+            // the previous TMA store of this warp must have drained the staging tile
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+            tmem_ld_wait();
+            if (plain) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(my_row + (((j >> 2) ^ sw) << 4)) =
+                    make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                float f[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) f[e] = __uint_as_float(v[j + e]);
+                if (p.bias != nullptr) {
+                  if (full) {
+                    const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                    f[0] += bv.x; f[1] += bv.y; f[2] += bv.z; f[3] += bv.w;
+                  } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                      if (col0 + j + e < p.n_valid) f[e] += __ldg(p.bias + col0 + j + e);
+                  }
+                }
+                if (p.relu) {
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) f[e] = fmaxf(f[e], 0.f);
+                }
+                *reinterpret_cast<float4*>(my_row + (((j >> 2) ^ sw) << 4)) =
+                    make_float4(f[0], f[1], f[2], f[3]);
+              }
+            }
+          } else {
+            uint32_t v0[32], v1[32];
+            tmem_ld_32x32(taddr + sl * 64, v0);            // both halves in flight before the wait
+            tmem_ld_32x32(taddr + sl * 64 + 32, v1);
+            // the previous TMA store of this warp must have drained the staging tile
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+            tmem_ld_wait();
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const uint32_t* v = half ? v1 : v0;
+              const int cb = col0 + half * 32;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j + e]);
+                if (!plain) {
+                  if (p.bias != nullptr) {
+                    if (full) {
+                      const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + cb + j));
+                      const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + cb + j + 4));
+                      f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                      f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+                    } else {
+#pragma unroll
+                      for (int e = 0; e < 8; ++e)
+                        if (cb + j + e < p.n_valid) f[e] += __ldg(p.bias + cb + j + e);
+                    }
+                  }
+                  if (p.relu) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+                  }
+                }
+                const int chunk = half * 4 + (j >> 3);
+                *reinterpret_cast<uint4*>(my_row + ((chunk ^ sw) << 4)) = pack8(f);
+              }
+            }
+          }
+          fence_proxy_async();             // generic-proxy smem writes -> visible to TMA
+          __syncwarp();
+          if (lane == 0) {
+            if (p.atomic)
+              asm volatile(
+                  "cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group"
+                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&mapC)),
+                  "r"(smem_u32(buf)), "r"(col0), "r"(c1), "r"(c2), "r"(c3)
+                  : "memory");
+            else
+              asm volatile(
+                  "cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group"
+                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&mapC)),
+                  "r"(smem_u32(buf)), "r"(col0), "r"(c1), "r"(c2), "r"(c3)
+                  : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
         }
-        store_chunk(p, f, row_off, col0, row_ok);
+      } else {
+        // direct-store fallback (outputs whose pitch is not a multiple of 16 bytes, odd boxes)
+        bool row_ok;
+        long long row_off;
+        if (p.kind == 0) {
+          const int dw = row % p.bw;
+          const int dh = (row / p.bw) % p.bh;
+          const int dn = row / (p.bw * p.bh);
+          const int w = tw * p.bw + dw, h = th * p.bh + dh, n = tn * p.bn + dn;
+          row_ok = (w < p.W) && (h < p.H) && (n < p.NB);
+          row_off = n * p.sN + h * p.sH + w * p.sW;
+        } else {
+          const int r = m_blk * kBM + row;
+          row_ok = r < p.m_valid;
+          row_off = static_cast<long long>(r) * p.sW;
+        }
+        for (int c = pi; c < p.BN / 32; c += 2) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          float f[32];
+          const int col0 = col_base + c * 32;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (p.bias != nullptr) {
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.n_valid) f[j] += __ldg(p.bias + col0 + j);
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          store_chunk(p, f, row_off, col0, row_ok);
+        }
       }
       tc_fence_before();
-      mbar_arrive(&bars->tmem_empty[acc]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (p.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   tc_fence_before();
@@ -341,6 +468,33 @@ static int make_map4(CUtensorMap* m, const void* base, const long long dims[4],
   return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
 }
 
+// Output tensor map (TMA store): bf16 (64-column slabs) or fp32 (32-column slabs).
+static int make_map_out(CUtensorMap* m, const void* base, const long long dims[4],
+                        const long long strides_el[3], const int box[4], bool f32) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return -1;
+  const int esz = f32 ? 4 : 2;
+  cuuint64_t gd[4] = {(cuuint64_t)dims[0], (cuuint64_t)dims[1], (cuuint64_t)dims[2],
+                      (cuuint64_t)dims[3]};
+  cuuint64_t gs[3] = {(cuuint64_t)strides_el[0] * esz, (cuuint64_t)strides_el[1] * esz,
+                      (cuuint64_t)strides_el[2] * esz};
+  cuuint32_t bx[4] = {(cuuint32_t)(f32 ? 32 : 64), (cuuint32_t)box[1], (cuuint32_t)box[2],
+                      (cuuint32_t)box[3]};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                   const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
+}
+static bool out_map_ok(const void* base, const long long strides_el[3], bool f32) {
+  const int esz = f32 ? 4 : 2;
+  if (reinterpret_cast<uintptr_t>(base) & 15) return false;
+  for (int i = 0; i < 3; ++i)
+    if ((strides_el[i] * esz) % 16) return false;
+  return true;
+}
+
 static int make_map2(CUtensorMap* m, const void* base, long long inner, long long outer,
                      long long ld_el, int box_inner, int box_outer) {
   EncodeTiledFn enc = get_encode();
@@ -367,26 +521,54 @@ static int num_sms() {
 }
 
 static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
-                  GemmParams& p, cudaStream_t stream) {
+                  const CUtensorMap* mapC, GemmParams& p, cudaStream_t stream) {
   const int stage_bytes = kBM * kBK * 2 + p.BN * kBK * 2;
-  int stages = (200 * 1024) / stage_bytes;
+  const int fixed = 2 * kStageOutBytes + (int)sizeof(Barriers) + 1024;
+  int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return -2;
   p.stages = stages;
-  const int smem = stages * stage_bytes + (int)sizeof(Barriers) + 1024;
-  static int configured = 0;
-  if (configured < smem) {
+  p.tma_store = mapC != nullptr ? 1 : 0;
+
+  const int smem = stages * stage_bytes + fixed;
+  static bool configured = false;
+  if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          227 * 1024);
     if (e != cudaSuccess) return (int)e;
-    configured = 227 * 1024;
+    configured = true;
   }
   const int total = p.tiles_m * p.tiles_n * p.splits;
   int grid = total < num_sms() ? total : num_sms();
   if (grid <= 0) return 0;
   tc_gemm_kernel<<<grid, kThreads, smem, stream>>>(mapsA[0], mapsA[1], mapsA[2], mapsA[3], mapsB[0],
-                                                   mapsB[1], mapsB[2], mapsB[3], p);
+                                                   mapsB[1], mapsB[2], mapsB[3],
+                                                   mapC != nullptr ? *mapC : mapsA[0], p);
   return (int)cudaGetLastError();
+}
+
+// Split the 128-row tile box (bw, bh, bn) into four 32-row sub-boxes, one per TMEM lane quarter
+// (rows are ordered w fastest, n slowest, so the split peels the slowest dimensions first).
+static bool quarter_box(GemmParams& p) {
+  int dims[3] = {p.bw, p.bh, p.bn};          // w, h, n
+  int f[3] = {1, 1, 1};
+  int need = 4;
+  for (int d = 2; d >= 0 && need > 1; --d) {
+    int g = 1;
+    while (g * 2 <= need && dims[d] % (g * 2) == 0) g *= 2;
+    f[d] = g;
+    need /= g;
+    if (g != dims[d] && need > 1) return false;   // a faster dimension may only be split once
+  }                                               // every slower one is fully split
+  if (need != 1) return false;
+  for (int d = 0; d < 3; ++d) p.qbox[d] = dims[d] / f[d];
+  for (int q = 0; q < 4; ++q) {
+    const int iw = q % f[0], ih = (q / f[0]) % f[1], in = q / (f[0] * f[1]);
+    p.qoff[q][0] = iw * p.qbox[0];
+    p.qoff[q][1] = ih * p.qbox[1];
+    p.qoff[q][2] = in * p.qbox[2];
+  }
+  return true;
 }
 
 static int pick_bn(int n) {
@@ -449,7 +631,16 @@ extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M,
   r = make_map2(&mb[0], B, K, N, ldb, kBK, p.BN);
   if (r) return r;
   mb[1] = mb[2] = mb[3] = mb[0];
-  return launch(ma, mb, p, (cudaStream_t)stream);
+  CUtensorMap mc;
+  long long dimsC[4] = {N, M, 1, 1};
+  long long strC[3] = {ldc, (long long)ldc * M, (long long)ldc * M};
+  const bool tma_out = out_map_ok(C, strC, out_fp32 != 0) && quarter_box(p);
+  if (tma_out) {
+    int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
+    r = make_map_out(&mc, C, dimsC, strC, qb, out_fp32 != 0);
+    if (r) return r;
+  }
+  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
 
 // C[M,N] fp32 (+)= A[Kr,M]^T * B[Kr,N]   (reduction over the Kr rows; both operands row-major
@@ -502,7 +693,16 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
   r = make_map4(&mb[0], B, dimsB, strB, box);
   if (r) return r;
   mb[1] = mb[2] = mb[3] = mb[0];
-  return launch(ma, mb, p, (cudaStream_t)stream);
+  CUtensorMap mc;
+  long long dimsC[4] = {N, M, 1, 1};
+  long long strC[3] = {ldc, (long long)ldc * M, (long long)ldc * M};
+  int boxC[4] = {32, 32, 1, 1};
+  const bool tma_out = out_map_ok(C, strC, true);
+  if (tma_out) {
+    r = make_map_out(&mc, C, dimsC, strC, boxC, true);
+    if (r) return r;
+  }
+  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
 
 // NHWC conv2d forward as implicit GEMM.  x: [NB, H, W, Cin] bf16, w: [Cout, R, S, Cin] bf16,
@@ -568,7 +768,16 @@ extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, i
   r = make_map2(&mb[0], w, (long long)p.ntaps * Cin, Cout, (long long)p.ntaps * Cin, kBK, p.BN);
   if (r) return r;
   mb[1] = mb[2] = mb[3] = mb[0];
-  return launch(ma, mb, p, (cudaStream_t)stream);
+  CUtensorMap mc;
+  long long dimsC[4] = {Cout, Wo, Ho, NB};
+  long long strC[3] = {p.sW, p.sH, p.sN};
+  const bool tma_out = out_map_ok(y, strC, false) && quarter_box(p);
+  if (tma_out) {
+    int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
+    r = make_map_out(&mc, y, dimsC, strC, qb, false);
+    if (r) return r;
+  }
+  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
 
 // NHWC conv2d weight gradient.  x: [NB,H,W,Cin], dy: [NB,Ho,Wo,Cout] (bf16), dw: [Cout,R,S,Cin] fp32
@@ -639,7 +848,16 @@ extern "C" int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw
             Tap{(int8_t)(py * 2 + px), (int8_t)((dx_ - px) / 2), (int8_t)((dy_ - py) / 2), 0};
       }
   }
-  return launch(ma, mb, p, (cudaStream_t)stream);
+  CUtensorMap mc;
+  long long dimsC[4] = {(long long)p.ntaps * Cin, Cout, 1, 1};
+  long long strC[3] = {p.sW, p.sW * Cout, p.sW * Cout};
+  int boxC[4] = {32, 32, 1, 1};
+  const bool tma_out = out_map_ok(dw, strC, true);
+  if (tma_out) {
+    r = make_map_out(&mc, dw, dimsC, strC, boxC, true);
+    if (r) return r;
+  }
+  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
 
 // Zero one phase view of a NHWC tensor (used when no filter tap reaches that phase).
@@ -717,7 +935,16 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx
       r = make_map2(&mb[0], wtb + wt_off, (long long)nt * Cout, Cin, (long long)nt * Cout, kBK, p.BN);
       if (r) return r;
       mb[1] = mb[2] = mb[3] = mb[0];
-      r = launch(ma, mb, p, (cudaStream_t)stream);
+      CUtensorMap mc;
+      long long dimsC[4] = {Cin, Wo, Ho, NB};
+      long long strC[3] = {p.sW, p.sH, p.sN};
+      const bool tma_out = out_map_ok(dxp, strC, false) && quarter_box(p);
+      if (tma_out) {
+        int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
+        r = make_map_out(&mc, dxp, dimsC, strC, qb, false);
+        if (r) return r;
+      }
+      r = launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
       if (r) return r;
       wt_off += (long long)nt * Cout * Cin;
     }

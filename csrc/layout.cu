@@ -83,21 +83,27 @@ stem_im2col_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ cols
     if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((long long)n * 3 + c) * H + h) * W + w];
     s[i] = v;
   }
+  // k -> offset inside the staged rows (filter row r, channel c, filter column ss); -1 = padding
+  __shared__ short lut[256];
+  for (int k = threadIdx.x; k < 256; k += blockDim.x) {
+    short o = -1;
+    if (k < 147) {
+      const int c = k % 3, ss = (k / 3) % 7, r = k / 21;
+      o = (short)((r * 3 + c) * PW + ss);
+    }
+    lut[k] = o;
+  }
   __syncthreads();
   const int kv = ldk / 8;                       // 16-byte vectors per output row
   __nv_bfloat16* out = cols + ((long long)n * Ho + ho) * Wo * ldk;
   for (int i = threadIdx.x; i < Wo * kv; i += blockDim.x) {
-    const int wo = i / kv, v8 = i % kv;
+    const int wo = i / kv, v8 = i - wo * kv;
+    const float* base = s + wo * 2;
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int k = v8 * 8 + j;
-      float val = 0.f;
-      if (k < 147) {
-        const int c = k % 3, ss = (k / 3) % 7, r = k / 21;
-        val = s[(r * 3 + c) * PW + wo * 2 + ss];
-      }
-      f[j] = val;
+      const short o = lut[v8 * 8 + j];
+      f[j] = o >= 0 ? base[o] : 0.f;
     }
     *reinterpret_cast<uint4*>(out + (long long)wo * ldk + v8 * 8) = pack8(f);
   }
