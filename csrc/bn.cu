@@ -37,21 +37,37 @@ static Slab make_slab(long long rows, int C, int target_blocks) {
   return s;
 }
 
-// Fold per-thread accumulators acc[NACC][8] over the row-lanes of the CTA; thread row-lane 0
-// ends up with the CTA totals for its channel group.
+// Fold the per-thread accumulators acc[NACC][8] of a CTA and add the CTA totals to
+// out[a * C + channel].  Lanes of a warp that own the same channel group are combined with
+// shuffles, the eight warps through shared memory, and the final sums / atomics are spread over
+// all threads (no serial tail on a few threads).
 template <int NACC>
-__device__ __forceinline__ void fold_rows(float (&acc)[NACC][8], int tx, int ty, int cols,
-                                          int rowlanes, float* smem) {
-  // smem layout: [ty][NACC*8][cols]  (conflict-free: consecutive tx -> consecutive banks)
-  for (int a = 0; a < NACC; ++a)
+__device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int cols, int C,
+                                             float* smem, float* __restrict__ out) {
+  constexpr int NV = NACC * 8;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = kBnThreads / 32;
+  for (int off = cols; off < 32; off <<= 1)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) smem[(ty * NACC * 8 + a * 8 + j) * cols + tx] = acc[a][j];
+    for (int a = 0; a < NACC; ++a)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[a][j] += __shfl_xor_sync(0xffffffffu, acc[a][j], off);
+  // with cols == 32 every warp is one row-lane; otherwise lanes < cols hold the warp partials
+  if (lane < cols) {
+#pragma unroll
+    for (int a = 0; a < NACC; ++a)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) smem[(warp * NV + a * 8 + j) * cols + tx] = acc[a][j];
+  }
   __syncthreads();
-  if (ty == 0) {
-    for (int r = 1; r < rowlanes; ++r)
-      for (int a = 0; a < NACC; ++a)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[a][j] += smem[(r * NACC * 8 + a * 8 + j) * cols + tx];
+  const int cv = C / 8;
+  for (int t = threadIdx.x; t < NV * cols; t += kBnThreads) {
+    const int v = t / cols, x = t - v * cols;
+    const int col = blockIdx.x * cols + x;
+    if (col >= cv) continue;
+    float s = 0.f;
+    for (int w = 0; w < nwarps; ++w) s += smem[(w * NV + v) * cols + x];
+    atomicAdd(out + (v >> 3) * C + col * 8 + (v & 7), s);
   }
 }
 
@@ -87,14 +103,7 @@ bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long
       for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] += f[j] * f[j]; }
     }
   }
-  fold_rows<2>(acc, tx, ty, cols, rowlanes, smem);
-  if (ty == 0 && col < cv) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(sums + col * 8 + j, acc[0][j]);
-      atomicAdd(sums + C + col * 8 + j, acc[1][j]);
-    }
-  }
+  fold_and_add<2>(acc, tx, cols, C, smem, sums);
 }
 
 template <bool kTrain>
@@ -224,14 +233,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
       }
     }
   }
-  fold_rows<2>(acc, tx, ty, cols, rowlanes, smem);
-  if (ty == 0 && col < cv) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(sums + col * 8 + j, acc[0][j]);
-      atomicAdd(sums + C + col * 8 + j, acc[1][j]);
-    }
-  }
+  fold_and_add<2>(acc, tx, cols, C, smem, sums);
 }
 
 __global__ void __launch_bounds__(kBnThreads)

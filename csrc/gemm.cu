@@ -43,7 +43,7 @@ struct GemmParams {
   int bw, bh, bn;           // box extents; bw*bh*bn == 128 (FPROP) or 64 (WGRAD)
   int tiles_w, tiles_h;     // boxes per row / per column of one image
   int W, H, NB;             // valid extents for masking
-  int cin_blocks;           // FPROP: Cin / 64 ; WGRAD: N tiles per tap
+  int cin_blocks;           // FPROP: Cin / 64 ; WGRAD: 64-wide N chunks per tap
   int ntaps;
   Tap taps[kMaxTaps];
   // epilogue
@@ -56,6 +56,12 @@ struct GemmParams {
   int qoff[4][3];           // origin of quarter q inside the tile box (w, h, n)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   const float* bias;
+};
+
+struct TmaMaps {
+  CUtensorMap a[kMaxMaps];
+  CUtensorMap b[kMaxMaps];
+  CUtensorMap c;
 };
 
 struct alignas(8) Barriers {
@@ -110,11 +116,7 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const float (&f
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
-               const __grid_constant__ CUtensorMap mapA2, const __grid_constant__ CUtensorMap mapA3,
-               const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
-               const __grid_constant__ CUtensorMap mapB2, const __grid_constant__ CUtensorMap mapB3,
-               const __grid_constant__ CUtensorMap mapC, const __grid_constant__ GemmParams p) {
+tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms.
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -130,9 +132,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&mapA0);
-    tma_prefetch_desc(&mapB0);
-    if (p.tma_store) tma_prefetch_desc(&mapC);
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b[0]);
+    if (p.tma_store) tma_prefetch_desc(&maps.c);
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&bars->full[i], 1);
       mbar_init(&bars->empty[i], 1);
@@ -153,9 +155,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
+    // One thread; the loops carry coordinates incrementally (no division per k-block) and use
+    // pre-computed 32-bit shared addresses, because this thread's instruction count per TMA
+    // issue bounds the rate at which short-K tiles can be fed.
     if (lane == 0) {
-      const CUtensorMap* mapsA[kMaxMaps] = {&mapA0, &mapA1, &mapA2, &mapA3};
-      const CUtensorMap* mapsB[kMaxMaps] = {&mapB0, &mapB1, &mapB2, &mapB3};
+      const uint32_t smem0 = smem_u32(smem);
+      const uint32_t full0 = smem_u32(&bars->full[0]);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -169,38 +174,66 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
           const int th = (m_blk / p.tiles_w) % p.tiles_h;
           const int tn = m_blk / (p.tiles_w * p.tiles_h);
           const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
-          for (int kb = kb0; kb < kb1; ++kb) {
-            const int tap = kb / p.cin_blocks;
-            const int cb = kb - tap * p.cin_blocks;
+          const int nb0 = n_blk * p.BN;
+          int kcoord = 0;
+#pragma unroll 1
+          for (int tap = 0; tap < p.ntaps; ++tap) {
             const Tap tp = p.taps[tap];
-            mbar_wait(&bars->empty[stage], phase ^ 1);
-            uint8_t* sa = smem + stage * stage_bytes;
-            uint8_t* sb = sa + a_stage_bytes;
-            mbar_expect_tx(&bars->full[stage], stage_bytes);
-            tma_load_4d(sa, mapsA[tp.map], &bars->full[stage], cb * kBK, w0 + tp.dw, h0 + tp.dh, n0);
-            tma_load_2d(sb, mapsB[0], &bars->full[stage], kb * kBK, n_blk * p.BN);
-            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            const CUtensorMap* ma = &maps.a[tp.map];
+            const int wt = w0 + tp.dw, ht = h0 + tp.dh;
+#pragma unroll 1
+            for (int cb = 0; cb < p.cin_blocks; ++cb, kcoord += kBK) {
+              mbar_wait(&bars->empty[stage], phase ^ 1);
+              const uint32_t sa = smem0 + stage * stage_bytes;
+              const uint32_t fb = full0 + stage * 8;
+              mbar_expect_tx_s(fb, stage_bytes);
+              tma_load_4d_s(sa, ma, fb, cb * kBK, wt, ht, n0);
+              tma_load_2d_s(sa + a_stage_bytes, &maps.b[0], fb, kcoord, nb0);
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
           }
         } else {
-          const int tap = n_blk / p.cin_blocks;
-          const int ct = n_blk - tap * p.cin_blocks;
-          const Tap tp = p.taps[tap];
-          const int nchunks_b = p.BN / 64;
+          // N is the stacked (tap, input-channel) axis in 64-wide chunks; a tile covers BN/64
+          // consecutive chunks, each with its own tap shift (and phase map for stride 2).
+          const int nchunks = p.BN >> 6;
+          const int gtotal = p.ntaps * p.cin_blocks;       // cin_blocks = 64-wide chunks per tap
+          const CUtensorMap* mb[4];
+          int cc0[4], cdw[4], cdh[4];
+          int nvalid = 0;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int g = n_blk * nchunks + c;
+            const bool ok = (c < nchunks) && (g < gtotal);
+            const int tap = ok ? g / p.cin_blocks : 0;
+            const Tap tp = p.taps[tap];
+            mb[c] = &maps.b[tp.map];
+            cc0[c] = ok ? (g - tap * p.cin_blocks) * 64 : 0;
+            cdw[c] = tp.dw;
+            cdh[c] = tp.dh;
+            if (ok) nvalid = c + 1;
+          }
+          const uint32_t tx_bytes = a_stage_bytes + nvalid * 8192;
+          const int m0 = m_blk * kBM;
+          // pixel box origin of k-block kb0, then advanced incrementally
+          int w0 = (kb0 % p.tiles_w) * p.bw;
+          int h0 = ((kb0 / p.tiles_w) % p.tiles_h) * p.bh;
+          int n0 = (kb0 / (p.tiles_w * p.tiles_h)) * p.bn;
+          const int wend = p.tiles_w * p.bw, hend = p.tiles_h * p.bh;
+#pragma unroll 1
           for (int kb = kb0; kb < kb1; ++kb) {
-            const int tw = kb % p.tiles_w;
-            const int th = (kb / p.tiles_w) % p.tiles_h;
-            const int tn = kb / (p.tiles_w * p.tiles_h);
-            const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
             mbar_wait(&bars->empty[stage], phase ^ 1);
-            uint8_t* sa = smem + stage * stage_bytes;
-            uint8_t* sb = sa + a_stage_bytes;
-            mbar_expect_tx(&bars->full[stage], stage_bytes);
+            const uint32_t sa = smem0 + stage * stage_bytes;
+            const uint32_t sb = sa + a_stage_bytes;
+            const uint32_t fb = full0 + stage * 8;
+            mbar_expect_tx_s(fb, tx_bytes);
             // A = dY^T : two 64-wide chunks of output channels, 64 pixels deep.
-            tma_load_4d(sa, mapsA[0], &bars->full[stage], m_blk * kBM, w0, h0, n0);
-            tma_load_4d(sa + 8192, mapsA[0], &bars->full[stage], m_blk * kBM + 64, w0, h0, n0);
-            for (int c = 0; c < nchunks_b; ++c)
-              tma_load_4d(sb + c * 8192, mapsB[tp.map], &bars->full[stage],
-                          ct * p.BN + c * 64, w0 + tp.dw, h0 + tp.dh, n0);
+            tma_load_4d_s(sa, &maps.a[0], fb, m0, w0, h0, n0);
+            tma_load_4d_s(sa + 8192, &maps.a[0], fb, m0 + 64, w0, h0, n0);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              if (c < nvalid) tma_load_4d_s(sb + c * 8192, mb[c], fb, cc0[c], w0 + cdw[c], h0 + cdh[c], n0);
+            w0 += p.bw;
+            if (w0 >= wend) { w0 = 0; h0 += p.bh; if (h0 >= hend) { h0 = 0; n0 += p.bn; } }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -366,13 +399,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
             if (p.atomic)
               asm volatile(
                   "cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group"
-                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&mapC)),
+                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&maps.c)),
                   "r"(smem_u32(buf)), "r"(col0), "r"(c1), "r"(c2), "r"(c3)
                   : "memory");
             else
               asm volatile(
                   "cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group"
-                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&mapC)),
+                  " [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(&maps.c)),
                   "r"(smem_u32(buf)), "r"(col0), "r"(c1), "r"(c2), "r"(c3)
                   : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -541,9 +574,10 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   const int total = p.tiles_m * p.tiles_n * p.splits;
   int grid = total < num_sms() ? total : num_sms();
   if (grid <= 0) return 0;
-  tc_gemm_kernel<<<grid, kThreads, smem, stream>>>(mapsA[0], mapsA[1], mapsA[2], mapsA[3], mapsB[0],
-                                                   mapsB[1], mapsB[2], mapsB[3],
-                                                   mapC != nullptr ? *mapC : mapsA[0], p);
+  TmaMaps maps;
+  for (int i = 0; i < kMaxMaps; ++i) { maps.a[i] = mapsA[i]; maps.b[i] = mapsB[i]; }
+  maps.c = mapC != nullptr ? *mapC : mapsA[0];
+  tc_gemm_kernel<<<grid, kThreads, smem, stream>>>(maps, p);
   return (int)cudaGetLastError();
 }
 
@@ -655,7 +689,7 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
   if ((lda % 8) || (ldb % 8)) return -3;
   GemmParams p{};
   p.kind = 1;
-  p.BN = (N > 64) ? 128 : 64;
+  p.BN = N >= 256 ? 256 : (N > 64 ? 128 : 64);
   p.tiles_m = (M + kBM - 1) / kBM;
   p.tiles_n = (N + p.BN - 1) / p.BN;
   p.kb_total = (Kr + 63) / 64;
@@ -672,7 +706,7 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
   p.bw = 64; p.bh = 1; p.bn = 1;
   p.tiles_w = p.kb_total; p.tiles_h = 1;
   p.W = Kr; p.H = 1; p.NB = 1;
-  p.cin_blocks = p.tiles_n;
+  p.cin_blocks = (N + 63) / 64;
   p.ntaps = 1;
   p.taps[0] = Tap{0, 0, 0, 0};
   p.C = C; p.sW = ldc; p.n_valid = N; p.m_valid = M;
@@ -790,16 +824,17 @@ extern "C" int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw
   const int Ho = H / stride, Wo = W / stride;
   GemmParams p{};
   p.kind = 1;
-  p.BN = (Cin % 128 == 0) ? 128 : 64;
+  const int n_total = R * R * Cin;
+  p.BN = n_total >= 256 ? 256 : (n_total >= 128 ? 128 : 64);
   pick_box(Wo, Ho, 64, &p.bw, &p.bh, &p.bn);
   p.tiles_w = Wo / p.bw;
   p.tiles_h = Ho / p.bh;
   const int tiles_nb = (NB + p.bn - 1) / p.bn;
   p.kb_total = p.tiles_w * p.tiles_h * tiles_nb;
   p.ntaps = R * R;
-  p.cin_blocks = Cin / p.BN;
+  p.cin_blocks = Cin / 64;
   p.tiles_m = (Cout + kBM - 1) / kBM;
-  p.tiles_n = p.ntaps * p.cin_blocks;
+  p.tiles_n = (n_total + p.BN - 1) / p.BN;
   const int out_tiles = p.tiles_m * p.tiles_n;
   int splits = (2 * num_sms() + out_tiles - 1) / out_tiles;
   if (splits > p.kb_total) splits = p.kb_total;

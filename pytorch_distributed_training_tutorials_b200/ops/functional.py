@@ -115,15 +115,16 @@ class _StemConv(torch.autograd.Function):
         wk = torch.zeros((weight.shape[0], NV.STEM_LDK), device=x.device, dtype=BF16)
         wk[:, :147] = weight.detach().reshape(weight.shape[0], 147)
         y = NV.gemm_tn(cols, wk)
-        ctx.save_for_backward(x, weight)
+        # the patch matrix is kept for the weight gradient (memory is cheap on a 180 GB part;
+        # re-gathering it costs a full extra pass over the input)
+        ctx.save_for_backward(cols, weight)
         return y.view(NB, H // 2, W // 2, weight.shape[0])
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight = ctx.saved_tensors
+        cols, weight = ctx.saved_tensors
         dw = None
         if ctx.needs_input_grad[1]:
-            cols = NV.stem_im2col(x.contiguous())            # recomputed: cheaper than keeping it
             dy2 = dy.reshape(-1, weight.shape[0]).contiguous()
             dwk = NV.gemm_nt_reduce(dy2, cols)               # [64, 160]
             dw = dwk[:, :147].reshape(weight.shape).contiguous()
