@@ -157,7 +157,8 @@ def run_ours(args, rank, world, local):
     model = resnet50(num_classes=args.classes)
     optimizer = FusedSGD(model.parameters(), lr=1e-3)
     trainer = Trainer(model, train_dataloader=None, optimizer=optimizer, gpu_id=local, wrap_ddp=True,
-                      ddp_kwargs=dict(allreduce=args.allreduce, comm_dtype=args.comm_dtype))
+                      ddp_kwargs=dict(allreduce=args.allreduce, comm_dtype=args.comm_dtype),
+                      cuda_graph=not args.no_graph)
     host_x, host_y = make_host_batches(2, args.batch_size, args.image, args.classes, seed=rank)
     dev_x = [x.to(device) for x in host_x]
     dev_y = [y.to(device) for y in host_y]
@@ -174,7 +175,7 @@ def run_ours(args, rank, world, local):
     launches = _lib.launch_count - launches0
     clocks = sampler.stop() if sampler else None
     e2e_ms, last_loss = timed_e2e_steps(trainer.step, host_x, host_y, args.steps, args.warmup, world, device)
-    info = {"model": "resnet50 (own NHWC bf16 kernels)", "loss": last_loss,
+    info = {"model": "resnet50 (own NHWC bf16 kernels)", "loss": last_loss, "cuda_graph": not args.no_graph,
             "ddp": trainer.model.get_logging_data() if hasattr(trainer.model, "get_logging_data") else None}
     group.destroy()
     return ms, e2e_ms, launches, clocks, info
@@ -258,6 +259,7 @@ def main() -> None:
     ap.add_argument("--classes", type=int, default=1000)
     ap.add_argument("--allreduce", default="auto", choices=["auto", "oneshot", "twoshot", "nvls", "nccl"])
     ap.add_argument("--comm-dtype", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

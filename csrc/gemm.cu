@@ -542,15 +542,16 @@ static int make_map2(CUtensorMap* m, const void* base, long long inner, long lon
   return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
 }
 
-static int g_num_sms = 0;
 static int num_sms() {
-  if (g_num_sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (cached[dev] <= 0) cached[dev] = 148;
   }
-  return g_num_sms;
+  return cached[dev];
 }
 
 static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
@@ -564,12 +565,15 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   p.tma_store = mapC != nullptr ? 1 : 0;
 
   const int smem = stages * stage_bytes + fixed;
-  static bool configured = false;
-  if (!configured) {
+  // function attributes are per device: opt in to the large dynamic smem once on each
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          227 * 1024);
     if (e != cudaSuccess) return (int)e;
-    configured = true;
+    configured[dev] = true;
   }
   const int total = p.tiles_m * p.tiles_n * p.splits;
   int grid = total < num_sms() ? total : num_sms();

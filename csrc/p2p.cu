@@ -182,4 +182,8 @@ extern "C" int b200dt_device_sm_count(void) {
   return n;
 }
 
+extern "C" const char* b200dt_error_string(int code) {
+  return cudaGetErrorString(static_cast<cudaError_t>(code));
+}
+
 extern "C" const char* b200dt_version(void) { return "b200dt 0.1 (sm_100a)"; }

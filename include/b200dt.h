@@ -182,6 +182,7 @@ int b200dt_p2p_gather_rows(const void* src, void* dst_peer, long long nbytes, fl
 
 /* ---------------------------------------------------------------- misc */
 int b200dt_device_sm_count(void);
+const char* b200dt_error_string(int cuda_error_code);
 const char* b200dt_version(void);
 
 #ifdef __cplusplus

@@ -11,7 +11,7 @@ from typing import Optional, Tuple
 import torch
 
 from .. import _lib
-from .._lib import check, lib, ptr, stream_ptr
+from .._lib import check, lib, on_device, ptr, stream_ptr
 
 BF16 = torch.bfloat16
 F32 = torch.float32
@@ -36,7 +36,7 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
         out = torch.empty((M, N), device=a.device, dtype=out_dtype)
     if bias is not None:
         _need(bias, F32, "bias")
-    with torch.cuda.device(a.device):
+    with on_device(a.device):
         check(lib().b200dt_gemm_tn_bf16(ptr(a), ptr(b), ptr(out), M, N, K, K, K, out.stride(0),
                                         ptr(bias), int(relu), int(out.dtype == F32),
                                         stream_ptr(a.device)), "gemm_tn")
@@ -52,7 +52,7 @@ def gemm_nt_reduce(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor]
         raise ValueError("gemm_nt_reduce: row mismatch or M/N % 8 != 0")
     if out is None:
         out = torch.empty((M, N), device=a.device, dtype=F32)
-    with torch.cuda.device(a.device):
+    with on_device(a.device):
         check(lib().b200dt_gemm_nt_reduce_bf16(ptr(a), ptr(b), ptr(out), M, N, R, M, N, out.stride(0), 0,
                                                stream_ptr(a.device)), "gemm_nt_reduce")
     return out
@@ -64,7 +64,7 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool =
     Cout, R, S, Cin2 = w.shape
     assert R == S and Cin == Cin2
     y = torch.empty((NB, H // stride, W // stride, Cout), device=x.device, dtype=BF16)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_conv2d_fprop_bf16(ptr(x), ptr(w), ptr(y), NB, H, W, Cin, Cout, R, stride,
                                              int(relu), stream_ptr(x.device)), "conv2d_fprop")
     return y
@@ -77,7 +77,7 @@ def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, R: int, stride: int = 1,
     Cout = dy.shape[-1]
     if out is None:
         out = torch.empty((Cout, R, R, Cin), device=x.device, dtype=F32)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_conv2d_wgrad_bf16(ptr(x), ptr(dy), ptr(out), NB, H, W, Cin, Cout, R, stride,
                                              stream_ptr(x.device)), "conv2d_wgrad")
     return out
@@ -87,7 +87,7 @@ def filter_transpose(w: torch.Tensor, stride: int = 1) -> torch.Tensor:
     _need(w, BF16, "w")
     Cout, R, S, Cin = w.shape
     wt = torch.empty(R * S * Cout * Cin, device=w.device, dtype=BF16)
-    with torch.cuda.device(w.device):
+    with on_device(w.device):
         check(lib().b200dt_filter_transpose_bf16(ptr(w), ptr(wt), Cin, Cout, R, stride,
                                                  stream_ptr(w.device)), "filter_transpose")
     return wt
@@ -98,7 +98,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt: torch.Tensor, x_shape, R: int, stride: in
     NB, H, W, Cin = x_shape
     Cout = dy.shape[-1]
     dx = torch.empty((NB, H, W, Cin), device=dy.device, dtype=BF16)
-    with torch.cuda.device(dy.device):
+    with on_device(dy.device):
         check(lib().b200dt_conv2d_dgrad_bf16(ptr(dy), ptr(wt), ptr(dx), NB, H, W, Cin, Cout, R, stride,
                                              stream_ptr(dy.device)), "conv2d_dgrad")
     return dx
@@ -114,7 +114,7 @@ def stem_im2col(x: torch.Tensor) -> torch.Tensor:
     NB, C, H, W = x.shape
     assert C == 3
     cols = torch.empty((NB * (H // 2) * (W // 2), STEM_LDK), device=x.device, dtype=BF16)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_stem_im2col(ptr(x), ptr(cols), NB, H, W, STEM_LDK, stream_ptr(x.device)),
               "stem_im2col")
     return cols
@@ -124,7 +124,7 @@ def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     _need(src, F32, "src")
     if out is None:
         out = torch.empty(src.shape, device=src.device, dtype=BF16)
-    with torch.cuda.device(src.device):
+    with on_device(src.device):
         check(lib().b200dt_cast_f32_to_bf16(ptr(src), ptr(out), src.numel(), stream_ptr(src.device)), "cast")
     return out
 
@@ -133,7 +133,7 @@ def transpose_bf16(src: torch.Tensor) -> torch.Tensor:
     _need(src, BF16, "src")
     r, c = src.shape
     out = torch.empty((c, r), device=src.device, dtype=BF16)
-    with torch.cuda.device(src.device):
+    with on_device(src.device):
         check(lib().b200dt_transpose_bf16(ptr(src), ptr(out), r, c, stream_ptr(src.device)), "transpose")
     return out
 
@@ -142,7 +142,7 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
     _need(x, F32, "x")
     NB, Cc, H, W = x.shape
     y = torch.empty((NB, H, W, Cc), device=x.device, dtype=BF16)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_nchw_f32_to_nhwc_bf16(ptr(x), ptr(y), NB, Cc, H, W, stream_ptr(x.device)), "nchw_to_nhwc")
     return y
 
@@ -151,7 +151,7 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
 def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
     rows, Cc = x2d.shape
     sums = torch.empty(2 * Cc, device=x2d.device, dtype=F32)
-    with torch.cuda.device(x2d.device):
+    with on_device(x2d.device):
         check(lib().b200dt_bn_stats(ptr(x2d), ptr(sums), rows, Cc, stream_ptr(x2d.device)), "bn_stats")
     return sums
 
@@ -162,7 +162,7 @@ def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, m
     y = torch.empty_like(x2d)
     save_mean = torch.empty(Cc, device=x2d.device, dtype=F32)
     save_invstd = torch.empty(Cc, device=x2d.device, dtype=F32)
-    with torch.cuda.device(x2d.device):
+    with on_device(x2d.device):
         check(lib().b200dt_bn_apply(ptr(x2d), ptr(residual), ptr(y), ptr(sums), ptr(gamma), ptr(beta),
                                     ptr(running_mean), ptr(running_var), ptr(save_mean), ptr(save_invstd),
                                     rows, Cc, eps, momentum, int(relu), stream_ptr(x2d.device)), "bn_apply")
@@ -172,7 +172,7 @@ def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, m
 def bn_apply_eval(x2d, residual, gamma, beta, mean, var, eps, relu) -> torch.Tensor:
     rows, Cc = x2d.shape
     y = torch.empty_like(x2d)
-    with torch.cuda.device(x2d.device):
+    with on_device(x2d.device):
         check(lib().b200dt_bn_apply_eval(ptr(x2d), ptr(residual), ptr(y), ptr(gamma), ptr(beta), ptr(mean),
                                          ptr(var), rows, Cc, eps, int(relu), stream_ptr(x2d.device)), "bn_eval")
     return y
@@ -187,7 +187,7 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
     dx = torch.empty_like(x2d)
     dgamma = torch.empty(Cc, device=dev, dtype=F32)
     dbeta = torch.empty(Cc, device=dev, dtype=F32)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         st = stream_ptr(dev)
         check(lib().b200dt_bn_bwd_reduce(ptr(dy2d), ptr(y2d), ptr(x2d), ptr(save_mean), ptr(save_invstd),
                                          ptr(sums), ptr(dres), rows, Cc, int(relu), st), "bn_bwd_reduce")
@@ -207,7 +207,7 @@ def maxpool_fwd(x: torch.Tensor):
     NB, H, W, Cc = x.shape
     y = torch.empty((NB, H // 2, W // 2, Cc), device=x.device, dtype=BF16)
     arg = torch.empty((NB, H // 2, W // 2, Cc), device=x.device, dtype=torch.uint8)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_maxpool3x3s2_fwd(ptr(x), ptr(y), ptr(arg), NB, H, W, Cc, stream_ptr(x.device)), "maxpool")
     return y, arg
 
@@ -215,7 +215,7 @@ def maxpool_fwd(x: torch.Tensor):
 def maxpool_bwd(dy: torch.Tensor, arg: torch.Tensor, x_shape) -> torch.Tensor:
     NB, H, W, Cc = x_shape
     dx = torch.empty(x_shape, device=dy.device, dtype=BF16)
-    with torch.cuda.device(dy.device):
+    with on_device(dy.device):
         check(lib().b200dt_maxpool3x3s2_bwd(ptr(dy), ptr(arg), ptr(dx), NB, H, W, Cc, stream_ptr(dy.device)), "maxpool_bwd")
     return dx
 
@@ -223,7 +223,7 @@ def maxpool_bwd(dy: torch.Tensor, arg: torch.Tensor, x_shape) -> torch.Tensor:
 def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
     NB, H, W, Cc = x.shape
     y = torch.empty((NB, Cc), device=x.device, dtype=BF16)
-    with torch.cuda.device(x.device):
+    with on_device(x.device):
         check(lib().b200dt_avgpool_fwd(ptr(x), ptr(y), NB, H * W, Cc, stream_ptr(x.device)), "avgpool")
     return y
 
@@ -231,7 +231,7 @@ def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
 def avgpool_bwd(dy: torch.Tensor, x_shape) -> torch.Tensor:
     NB, H, W, Cc = x_shape
     dx = torch.empty(x_shape, device=dy.device, dtype=BF16)
-    with torch.cuda.device(dy.device):
+    with on_device(dy.device):
         check(lib().b200dt_avgpool_bwd(ptr(dy), ptr(dx), NB, H * W, Cc, stream_ptr(dy.device)), "avgpool_bwd")
     return dx
 
@@ -258,7 +258,7 @@ def _loss_common(kind: str, pred: torch.Tensor, other, grad_scale: float, want_g
         raise ValueError("loss input must be contiguous fp32 or bf16")
     loss = torch.empty((), device=dev, dtype=F32)
     grad = torch.empty_like(pred) if want_grad else None
-    with torch.cuda.device(dev):
+    with on_device(dev):
         sc = loss_scratch(dev)
         st = stream_ptr(dev)
         L = lib()

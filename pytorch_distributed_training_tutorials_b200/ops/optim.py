@@ -35,14 +35,19 @@ class _DeviceTable:
         key = tuple(tuple(r) for r in rows)
         if key == self.key:
             return
-        meta = torch.tensor(rows, dtype=torch.int64)
         ch = []
         for ti, r in enumerate(rows):
             n = r[3]
             ch.extend((ti, s) for s in range(0, n, CHUNK))
-        chunks = torch.tensor(ch, dtype=torch.int32)
-        self.meta = meta.to(self.device, non_blocking=False)
-        self.chunks = chunks.to(self.device, non_blocking=False)
+        # pinned staging + async copies on the current stream: legal while a CUDA graph is being
+        # captured (the copies become memcpy nodes; the pinned buffers are never rewritten unless
+        # the pointers change, which they do not between replays)
+        self._meta_host = torch.tensor(rows, dtype=torch.int64).pin_memory()
+        self._chunks_host = torch.tensor(ch, dtype=torch.int32).pin_memory()
+        self.meta = torch.empty_like(self._meta_host, device=self.device)
+        self.chunks = torch.empty_like(self._chunks_host, device=self.device)
+        self.meta.copy_(self._meta_host, non_blocking=True)
+        self.chunks.copy_(self._chunks_host, non_blocking=True)
         self.n_chunks = len(ch)
         self.key = key
 
@@ -153,6 +158,9 @@ class FusedAdam(_FusedBase):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        if torch.cuda.is_available() and torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("FusedAdam keeps its step count on the host and cannot be captured in a CUDA "
+                               "graph; use FusedSGD under GraphedTrainStep")
         for gi, group in enumerate(self.param_groups):
             b1, b2 = group["betas"]
             t = None

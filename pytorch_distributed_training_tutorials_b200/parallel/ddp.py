@@ -251,8 +251,9 @@ class DistributedDataParallel(nn.Module):
             cur = torch.cuda.current_stream(self.device)
             self._ready_event.record(cur)
             self._side_stream.wait_event(self._ready_event)
-            for g in grads:
-                g.record_stream(self._side_stream)
+            if not torch.cuda.is_current_stream_capturing():
+                for g in grads:
+                    g.record_stream(self._side_stream)
             b.table.bind(grads, self._side_stream)
             coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
                         max_blocks=self.max_comm_blocks)

@@ -29,7 +29,7 @@ class Trainer:
     def __init__(self, model: torch.nn.Module, train_dataloader: DataLoader,
                  optimizer: torch.optim.Optimizer, gpu_id: Optional[int] = None,
                  loss_fn: Optional[Callable] = None, wrap_ddp: bool = True, ddp_kwargs: Optional[dict] = None,
-                 log_every: int = 0) -> None:
+                 log_every: int = 0, cuda_graph: bool = False) -> None:
         if gpu_id is None:
             gpu_id = int(os.environ.get("LOCAL_RANK", "0"))
         self.gpu_id = gpu_id
@@ -41,12 +41,22 @@ class Trainer:
         self.log_every = log_every
         self.last_loss: Optional[torch.Tensor] = None
         self.global_step = 0
+        self.cuda_graph = cuda_graph and self.device.type == "cuda"
+        self._graphed = None
         if wrap_ddp:
             from .parallel.ddp import DistributedDataParallel
             ids = [gpu_id] if self.device.type == "cuda" else None
             self.model = DistributedDataParallel(self.model, device_ids=ids, **(ddp_kwargs or {}))
 
     def _run_batch(self, xs, ys):
+        if self.cuda_graph:
+            if self._graphed is None:
+                from .utils.graph import GraphedTrainStep
+                self._graphed = GraphedTrainStep(self.model, self.loss_fn, self.optimizer, xs, ys)
+            if self._graphed.matches(xs, ys):
+                self.last_loss = self._graphed(xs, ys)
+                self.global_step += 1
+                return self.last_loss
         self.optimizer.zero_grad()
         output = self.model(xs)
         loss = self.loss_fn(output, ys)
