@@ -182,6 +182,16 @@ extern "C" int b200dt_device_sm_count(void) {
   return n;
 }
 
+// Plain cudaMemcpyAsync host->device for the small pointer / chunk tables.  Called through the C
+// ABI so that torch's pinned-memory allocator never records an event for the source buffer: an
+// event recorded while a CUDA graph is being captured cannot be queried later and would poison
+// that allocator.
+extern "C" int b200dt_memcpy_h2d_async(void* dst, const void* src_pinned, long long nbytes, void* stream) {
+  if (nbytes <= 0) return 0;
+  return (int)cudaMemcpyAsync(dst, src_pinned, (size_t)nbytes, cudaMemcpyHostToDevice,
+                              (cudaStream_t)stream);
+}
+
 extern "C" const char* b200dt_error_string(int code) {
   return cudaGetErrorString(static_cast<cudaError_t>(code));
 }

@@ -92,6 +92,15 @@ class Reducer {
       : params_(std::move(params)), on_bucket_ready_(std::move(on_bucket_ready)),
         on_finalize_(std::move(on_finalize)) {
     set_buckets(std::move(buckets));
+    install_hooks();
+  }
+
+  // (Re-)register the post-hooks.  AccumulateGrad nodes remember the CUDA stream that was current
+  // when they were created; calling this under a side stream (after remove_hooks() released the
+  // old nodes) re-creates them there, which whole-step CUDA graph capture requires: a node bound
+  // to the legacy default stream cannot take part in a capture.
+  void install_hooks() {
+    remove_hooks();
     for (size_t i = 0; i < params_.size(); ++i) {
       auto& p = params_[i];
       TORCH_CHECK(p.requires_grad(), "every reducer parameter must require grad");
@@ -263,5 +272,6 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("buckets", &Reducer::buckets)
       .def("finalized", &Reducer::finalized)
       .def("remove_hooks", &Reducer::remove_hooks)
+      .def("install_hooks", &Reducer::install_hooks)
       .def("stats", &Reducer::stats);
 }

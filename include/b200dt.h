@@ -181,6 +181,8 @@ int b200dt_p2p_gather_rows(const void* src, void* dst_peer, long long nbytes, fl
                            int is_f32, void* stream);
 
 /* ---------------------------------------------------------------- misc */
+/* cudaMemcpyAsync(H2D) from caller-owned pinned memory (table uploads; capturable). */
+int b200dt_memcpy_h2d_async(void* dst, const void* src_pinned, long long nbytes, void* stream);
 int b200dt_device_sm_count(void);
 const char* b200dt_error_string(int cuda_error_code);
 const char* b200dt_version(void);

@@ -75,6 +75,7 @@ _SIGS = {
     "b200dt_p2p_broadcast": [vp, vp, i32, i64, vp],
     "b200dt_p2p_reduce_f32": [vp, vp, i32, i64, f32, i32, vp],
     "b200dt_p2p_gather_rows": [vp, vp, i64, vp, i32, vp],
+    "b200dt_memcpy_h2d_async": [vp, vp, i64, vp],
 }
 
 
@@ -120,7 +121,7 @@ def lib() -> "_Counted":
         handle.b200dt_version.restype = C.c_char_p
         handle.b200dt_error_string.restype = C.c_char_p
         handle.b200dt_error_string.argtypes = [i32]
-        _lib = _Counted(handle, [n for n in _SIGS if n != "b200dt_enable_peer_access"])
+        _lib = _Counted(handle, [n for n in _SIGS if n not in ("b200dt_enable_peer_access", "b200dt_memcpy_h2d_async")])
         return _lib
 
 
@@ -192,3 +193,49 @@ def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
 def u64_array(values) -> C.Array:
     arr = (u64 * len(values))(*[int(v) for v in values])
     return arr
+
+
+class PinnedUploader:
+    """Stream-ordered upload of small host tables through a ring of pinned staging buffers.
+
+    Outside graph capture a slot is reused only after the event recorded behind its last copy has
+    completed.  During capture no event is recorded (it could never be queried afterwards); the
+    slot is frozen instead, because the captured memcpy node re-reads it on every replay."""
+
+    def __init__(self, slots: int = 4) -> None:
+        self._slots = []          # [buffer(uint8, pinned), event or None, frozen]
+        self._max_free = slots
+
+    def _acquire(self, nbytes: int, capturing: bool):
+        if capturing:
+            # no event may be queried while a capture is in progress: take a fresh, dedicated slot
+            s = [torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory(), None, True]
+            self._slots.append(s)
+            return s
+        for s in self._slots:
+            if s[2] or s[0].numel() < nbytes:
+                continue
+            if s[1] is None or s[1].query():
+                return s
+        free = [s for s in self._slots if not s[2] and s[0].numel() >= nbytes]
+        if len(free) >= self._max_free:
+            free[0][1].synchronize()
+            return free[0]
+        s = [torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory(), None, False]
+        self._slots.append(s)
+        return s
+
+    def upload(self, dst: torch.Tensor, src_cpu: torch.Tensor, stream: "torch.cuda.Stream") -> None:
+        nbytes = src_cpu.numel() * src_cpu.element_size()
+        assert dst.numel() * dst.element_size() >= nbytes
+        capturing = torch.cuda.is_current_stream_capturing()
+        slot = self._acquire(nbytes, capturing)
+        slot[0][:nbytes].copy_(src_cpu.contiguous().view(torch.uint8).view(-1))
+        check(lib().b200dt_memcpy_h2d_async(dst.data_ptr(), slot[0].data_ptr(), nbytes, stream.cuda_stream),
+              "table upload")
+        if capturing:
+            slot[2] = True
+        else:
+            if slot[1] is None:
+                slot[1] = torch.cuda.Event()
+            slot[1].record(stream)

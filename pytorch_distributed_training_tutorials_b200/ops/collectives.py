@@ -118,8 +118,8 @@ class TensorTable:
             raw[3 * i + 1] = ln                          # {int32 len, int32 pad}
             raw[3 * i + 2] = o
         self.chunks = raw.to(device)
-        self._host = torch.empty(len(self.numels) * 2, dtype=torch.int64).pin_memory() \
-            if torch.cuda.is_available() else torch.empty(len(self.numels) * 2, dtype=torch.int64)
+        self._host = torch.empty(len(self.numels) * 2, dtype=torch.int64)
+        self._uploader = _lib.PinnedUploader()
         self.tensors = torch.zeros(len(self.numels) * 2, dtype=torch.int64, device=device)
         self._ptr_key = None
 
@@ -135,8 +135,7 @@ class TensorTable:
             assert t.numel() == self.numels[i] and t.is_contiguous()
             self._host[2 * i] = t.data_ptr()
             self._host[2 * i + 1] = t.numel()
-        with torch.cuda.stream(stream):
-            self.tensors.copy_(self._host, non_blocking=True)
+        self._uploader.upload(self.tensors, self._host, stream)
         self._ptr_key = key
 
 

@@ -30,6 +30,7 @@ class _DeviceTable:
         self.meta = None
         self.chunks = None
         self.n_chunks = 0
+        self._uploader = _lib.PinnedUploader()
 
     def update(self, rows: List[List[int]]) -> None:
         key = tuple(tuple(r) for r in rows)
@@ -39,15 +40,17 @@ class _DeviceTable:
         for ti, r in enumerate(rows):
             n = r[3]
             ch.extend((ti, s) for s in range(0, n, CHUNK))
-        # pinned staging + async copies on the current stream: legal while a CUDA graph is being
-        # captured (the copies become memcpy nodes; the pinned buffers are never rewritten unless
-        # the pointers change, which they do not between replays)
-        self._meta_host = torch.tensor(rows, dtype=torch.int64).pin_memory()
-        self._chunks_host = torch.tensor(ch, dtype=torch.int32).pin_memory()
-        self.meta = torch.empty_like(self._meta_host, device=self.device)
-        self.chunks = torch.empty_like(self._chunks_host, device=self.device)
-        self.meta.copy_(self._meta_host, non_blocking=True)
-        self.chunks.copy_(self._chunks_host, non_blocking=True)
+        # stream-ordered uploads from library-owned pinned staging (capturable: they become memcpy
+        # nodes of the graph, and torch's pinned allocator never sees them)
+        meta_host = torch.tensor(rows, dtype=torch.int64)
+        chunks_host = torch.tensor(ch, dtype=torch.int32)
+        if self.meta is None or self.meta.numel() != meta_host.numel():
+            self.meta = torch.empty(meta_host.shape, dtype=torch.int64, device=self.device)
+        if self.chunks is None or self.chunks.numel() != chunks_host.numel():
+            self.chunks = torch.empty(chunks_host.shape, dtype=torch.int32, device=self.device)
+        stream = torch.cuda.current_stream(self.device)
+        self._uploader.upload(self.meta, meta_host, stream)
+        self._uploader.upload(self.chunks, chunks_host, stream)
         self.n_chunks = len(ch)
         self.key = key
 

@@ -316,6 +316,11 @@ class DistributedDataParallel(nn.Module):
             self.require_backward_grad_sync = old
             self._reducer.set_require_sync(old)
 
+    def rebind_autograd_hooks(self) -> None:
+        """Re-create the parameters' gradient accumulators under the CURRENT stream (call inside a
+        side-stream context before capturing the step in a CUDA graph)."""
+        self._reducer.install_hooks()
+
     def get_logging_data(self) -> dict:
         d = dict(self._reducer.stats())
         d.update(self._stats)

@@ -35,6 +35,10 @@ class GraphedTrainStep:
         side = torch.cuda.Stream(self.device)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
+            # gradient accumulators must not be bound to the legacy default stream (see the reducer)
+            for m in model.modules():
+                if hasattr(m, "rebind_autograd_hooks"):
+                    m.rebind_autograd_hooks()
             for _ in range(max(warmup, 3)):      # DDP needs >= 2 eager iterations to settle its buckets
                 self._eager()
         cur.wait_stream(side)
