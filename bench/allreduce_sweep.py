@@ -30,7 +30,7 @@ def timed(fn, iters, dev):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=int, default=1024)
-    ap.add_argument("--blocks", type=int, default=64)
+    ap.add_argument("--blocks", type=int, default=128)
     args = ap.parse_args()
     st = group.init(backend="nccl")
     dev, world, rank = st.device, st.world_size, st.rank
@@ -49,11 +49,11 @@ def main():
         for m in modes:
             if m == "oneshot" and size > (8 << 20):
                 continue
-            table = coll.TensorTable([n], dev, False, False)
+            table = coll.TensorTable([n], dev, False, False, target_blocks=args.blocks)
             table.bind([x], stream)
             row[m + "_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks), iters, dev)
         if size >= (1 << 20):
-            table = coll.TensorTable([n], dev, True, False)
+            table = coll.TensorTable([n], dev, True, False, target_blocks=args.blocks)
             table.bind([x], stream)
             m = "nvls" if arena.has_multicast else "twoshot"
             row[m + "_bf16wire_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks), iters, dev)

@@ -130,10 +130,10 @@ __device__ __forceinline__ void store8_tensor(void* base, long long idx, int bf1
 // Staging is always 16-byte aligned and padded to 8 elements.
 __device__ __forceinline__ void load8_stage(const void* stage, long long e, int bf16, float (&f)[8]) {
   if (bf16) {
-    unpack8(ld_sys_v4(reinterpret_cast<const __nv_bfloat16*>(stage) + e), f);
+    unpack8(ld_cg_v4(reinterpret_cast<const __nv_bfloat16*>(stage) + e), f);
   } else {
     const float* p = reinterpret_cast<const float*>(stage) + e;
-    const uint4 a = ld_sys_v4(p), b = ld_sys_v4(p + 4);
+    const uint4 a = ld_cg_v4(p), b = ld_cg_v4(p + 4);
     f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y);
     f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
     f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y);
@@ -152,7 +152,106 @@ __device__ __forceinline__ void store8_stage(void* stage, long long e, int bf16,
   }
 }
 
-template <int kMode>
+// Sum one 8-element group over all ranks' staging buffers.  Every peer load is issued before the
+// first add (up to 16 independent 16-byte NVLink loads in flight per thread); the summation order
+// is rank 0..world-1 on every rank, so all ranks produce bit-identical results.
+__device__ __forceinline__ void reduce_group(const CollArgs& a, long long e, float (&acc)[8]) {
+  uint4 lo[B200DT_MAX_WORLD], hi[B200DT_MAX_WORLD];
+  if (a.wire_bf16) {
+#pragma unroll
+    for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+      if (r < a.world)
+        lo[r] = ld_cg_v4(reinterpret_cast<const __nv_bfloat16*>(
+                              reinterpret_cast<const char*>(a.bufs[r]) + a.stage_base) + e);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+      if (r < a.world) {
+        float f[8];
+        unpack8(lo[r], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+  } else {
+#pragma unroll
+    for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+      if (r < a.world) {
+        const float* p = reinterpret_cast<const float*>(
+                             reinterpret_cast<const char*>(a.bufs[r]) + a.stage_base) + e;
+        lo[r] = ld_cg_v4(p);
+        hi[r] = ld_cg_v4(p + 4);
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+      if (r < a.world) {
+        acc[0] += __uint_as_float(lo[r].x); acc[1] += __uint_as_float(lo[r].y);
+        acc[2] += __uint_as_float(lo[r].z); acc[3] += __uint_as_float(lo[r].w);
+        acc[4] += __uint_as_float(hi[r].x); acc[5] += __uint_as_float(hi[r].y);
+        acc[6] += __uint_as_float(hi[r].z); acc[7] += __uint_as_float(hi[r].w);
+      }
+  }
+}
+
+// Two-shot reduce + push for one chunk with a compile-time world size.  Works on 16-byte vectors so
+// that every warp-level load / store touches one contiguous 512-byte run (no sector is requested
+// twice over NVLink), and keeps 16 independent peer loads in flight per thread regardless of W.
+template <int W>
+__device__ __forceinline__ void twoshot_chunk(const CollArgs& a, const CollChunk& ch) {
+  constexpr int VU = 16 / W;
+  const int esz = a.wire_bf16 ? 2 : 4;
+  const long long nvec = (long long)((ch.len + 7) / 8) * 8 * esz / 16;
+  const long long per = (nvec + W - 1) / W;
+  const long long v_beg = a.rank * per;
+  const long long v_end = min(nvec, v_beg + per);
+  const long long byte0 = a.stage_base + ch.stage_off * esz;
+  for (long long v0 = v_beg + threadIdx.x; v0 < v_end; v0 += (long long)VU * blockDim.x) {
+    uint4 in[VU][W];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long v = v0 + (long long)u * blockDim.x;
+      if (v < v_end) {
+#pragma unroll
+        for (int r = 0; r < W; ++r)
+          in[u][r] = ld_cg_v4(reinterpret_cast<const char*>(a.bufs[r]) + byte0 + v * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long v = v0 + (long long)u * blockDim.x;
+      if (v >= v_end) continue;
+      uint4 out;
+      if (a.wire_bf16) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {          // rank order: identical result on every rank
+          float f[8];
+          unpack8(in[u][r], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+        out = pack8(acc);
+      } else {
+        float x = 0.f, y = 0.f, z = 0.f, w = 0.f;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+          x += __uint_as_float(in[u][r].x); y += __uint_as_float(in[u][r].y);
+          z += __uint_as_float(in[u][r].z); w += __uint_as_float(in[u][r].w);
+        }
+        out = make_uint4(__float_as_uint(x), __float_as_uint(y), __float_as_uint(z), __float_as_uint(w));
+      }
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        st_v4(reinterpret_cast<char*>(a.bufs[r]) + byte0 + v * 16, out);
+    }
+  }
+}
+
+template <int kMode, int W>     // W: compile-time world size for the two-shot fast path, 0 = generic
 __global__ void __launch_bounds__(kCollThreads)
 coll_kernel(const __grid_constant__ CollArgs a) {
   const int esz_t = a.tensor_bf16 ? 2 : 4;
@@ -165,6 +264,31 @@ coll_kernel(const __grid_constant__ CollArgs a) {
       const CollTensor tt = a.tensors[ch.tensor];
       const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
       const int groups = (ch.len + 7) / 8;
+      if (kMode != kBcast) {
+        // four groups per thread: all loads are issued before the first dependent store
+        for (int g0 = threadIdx.x; g0 < groups; g0 += 4 * blockDim.x) {
+          float f[4][8];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int g = g0 + u * blockDim.x;
+            if (g < groups)
+              load8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, min(8, ch.len - g * 8),
+                           aligned, f[u]);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int g = g0 + u * blockDim.x;
+            if (g < groups) {
+              if (a.scale != 1.f) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[u][j] *= a.scale;
+              }
+              store8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f[u]);
+            }
+          }
+        }
+        continue;
+      }
       for (int g = threadIdx.x; g < groups; g += blockDim.x) {
         float f[8];
         const int n = min(8, ch.len - g * 8);
@@ -210,16 +334,7 @@ coll_kernel(const __grid_constant__ CollArgs a) {
       const int groups = (ch.len + 7) / 8;
       for (int g = threadIdx.x; g < groups; g += blockDim.x) {
         float acc[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        // Fixed summation order (rank 0..world-1) on every rank: results are bit-identical.
-        for (int r = 0; r < a.world; ++r) {
-          float f[8];
-          load8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, ch.stage_off + g * 8,
-                      a.wire_bf16, f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += f[j];
-        }
+        reduce_group(a, ch.stage_off + g * 8, acc);
         const int n = min(8, ch.len - g * 8);
         store8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, acc);
       }
@@ -232,6 +347,10 @@ coll_kernel(const __grid_constant__ CollArgs a) {
   if (kMode == kTwoShot || kMode == kNvls) {
     for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
       const CollChunk ch = a.chunks[c];
+      if (kMode == kTwoShot && W > 0) {
+        twoshot_chunk<(W > 0 ? W : 2)>(a, ch);
+        continue;
+      }
       const int groups = (ch.len + 7) / 8;
       const int per = (groups + a.world - 1) / a.world;      // groups owned by each rank
       const int g0 = a.rank * per;
@@ -253,18 +372,11 @@ coll_kernel(const __grid_constant__ CollArgs a) {
           }
         } else {
           float acc[8];
+          reduce_group(a, e, acc);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-          for (int r = 0; r < a.world; ++r) {
-            float f[8];
-            load8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, e, a.wire_bf16, f);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] += f[j];
-          }
-          for (int r = 0; r < a.world; ++r) {
-            const int dst = (a.rank + r) % a.world;     // spread the writes over the links
-            store8_stage(reinterpret_cast<char*>(a.bufs[dst]) + a.stage_base, e, a.wire_bf16, acc);
-          }
+          for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+            if (r < a.world)
+              store8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, e, a.wire_bf16, acc);
         }
       }
     }
@@ -277,11 +389,19 @@ coll_kernel(const __grid_constant__ CollArgs a) {
     const CollTensor tt = a.tensors[ch.tensor];
     const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
     const int groups = (ch.len + 7) / 8;
-    for (int g = threadIdx.x; g < groups; g += blockDim.x) {
-      float f[8];
-      load8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f);
-      const int n = min(8, ch.len - g * 8);
-      store8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, n, aligned, f);
+    for (int g0 = threadIdx.x; g0 < groups; g0 += 4 * blockDim.x) {
+      float f[4][8];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int g = g0 + u * blockDim.x;
+        if (g < groups) load8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int g = g0 + u * blockDim.x;
+        if (g < groups)
+          store8_tensor(tt.ptr, (long long)ch.start + g * 8, a.tensor_bf16, min(8, ch.len - g * 8), aligned, f[u]);
+      }
     }
   }
   if (kMode == kBcast && a.world > 1) {
@@ -360,10 +480,15 @@ extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t
   a.spin_limit = 1ull << 26;     // ~ tens of seconds of polling before giving up
   cudaStream_t st = (cudaStream_t)stream;
   switch (mode) {
-    case kOneShot: coll_kernel<kOneShot><<<grid, kCollThreads, 0, st>>>(a); break;
-    case kTwoShot: coll_kernel<kTwoShot><<<grid, kCollThreads, 0, st>>>(a); break;
-    case kNvls: coll_kernel<kNvls><<<grid, kCollThreads, 0, st>>>(a); break;
-    case kBcast: coll_kernel<kBcast><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kOneShot: coll_kernel<kOneShot, 0><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kTwoShot:
+      if (world == 8) coll_kernel<kTwoShot, 8><<<grid, kCollThreads, 0, st>>>(a);
+      else if (world == 4) coll_kernel<kTwoShot, 4><<<grid, kCollThreads, 0, st>>>(a);
+      else if (world == 2) coll_kernel<kTwoShot, 2><<<grid, kCollThreads, 0, st>>>(a);
+      else coll_kernel<kTwoShot, 0><<<grid, kCollThreads, 0, st>>>(a);
+      break;
+    case kNvls: coll_kernel<kNvls, 0><<<grid, kCollThreads, 0, st>>>(a); break;
+    case kBcast: coll_kernel<kBcast, 0><<<grid, kCollThreads, 0, st>>>(a); break;
     default: return -3;
   }
   return (int)cudaGetLastError();

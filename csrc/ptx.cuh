@@ -245,6 +245,16 @@ __device__ __forceinline__ uint4 ld_sys_v4(const void* p) {
                : "memory");
   return r;
 }
+// L2-only (L1-bypassing) 16-byte load: used for staging buffers after the acquire of the
+// cross-GPU barrier; cheaper than a system-scope relaxed load and never served from a stale L1 line.
+__device__ __forceinline__ uint4 ld_cg_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 __device__ __forceinline__ void st_v4(void* p, const uint4& v) {
   asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
                "r"(v.w)

@@ -78,7 +78,9 @@ def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> st
         if requested == "nvls" and not arena.has_multicast:
             raise RuntimeError("allreduce='nvls' requested but the arena has no multicast mapping")
         return requested
-    if nbytes <= ONESHOT_MAX_BYTES:
+    # one-shot pulls (world-1) x the payload into every rank: only worth it for latency-bound
+    # messages, and the break-even shrinks with the number of peers (measured: profiles/)
+    if nbytes <= (ONESHOT_MAX_BYTES if arena.world <= 2 else 16 * 1024):
         return "oneshot"
     return "nvls" if arena.has_multicast else "twoshot"
 
@@ -98,6 +100,10 @@ class TensorTable:
         chunk = CHUNK_ELEMS
         while chunk > 2048 and total // chunk < target_blocks:
             chunk //= 2
+        # ... and large payloads use bigger chunks, so the per-chunk table fetch (two dependent
+        # global loads) is amortised over megabytes instead of 64 KB
+        while chunk < (1 << 20) and total // chunk > 8 * target_blocks:
+            chunk *= 2
         self.chunk_elems = chunk
         rows = []
         off = 0
@@ -157,7 +163,7 @@ def all_reduce_(tensors: List[torch.Tensor], arena: SymmetricArena, mode: str = 
     dev = arena.device
     stream = stream or torch.cuda.current_stream(dev)
     tb16 = tensors[0].dtype == torch.bfloat16
-    table = TensorTable([t.numel() for t in tensors], dev, wire_bf16, tb16)
+    table = TensorTable([t.numel() for t in tensors], dev, wire_bf16, tb16, target_blocks=max_blocks)
     table.bind(tensors, stream)
     m = pick_mode(table.stage_bytes, arena, mode)
     launch(m, arena, table, scale, stream, max_blocks=max_blocks)

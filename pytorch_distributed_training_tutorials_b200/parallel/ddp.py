@@ -211,7 +211,7 @@ class DistributedDataParallel(nn.Module):
                 from ..ops import collectives as coll
                 tb16 = self._params[ids[0]].dtype == torch.bfloat16
                 b.table = coll.TensorTable([self._params[j].numel() for j in ids], self.device,
-                                           self.comm_dtype == "bf16", tb16)
+                                           self.comm_dtype == "bf16", tb16, target_blocks=self.max_comm_blocks)
                 b.mode = coll.pick_mode(b.table.stage_bytes, self._arena, self.allreduce)
             out.append(b)
         return out
