@@ -1,0 +1,52 @@
+"""Single-process multi-GPU DataParallel (counterpart of /root/reference/01.data_parallel.ipynb).
+
+    python examples/data_parallel_demo.py [--devices cpu,cpu,cpu,cpu]
+
+``RandomDataset(32, 1024)`` -> batches of 32 -> ``SampleModel`` (``Linear(32, 2)`` that prints the shape
+it sees).  On 4 GPUs every ``[32, 32]`` batch shows up as 4 x ``[8, 32]`` inside the replicas and comes
+back as ``[32, 2]`` (01.data_parallel.ipynb:300-473).  ``--devices`` accepts CPU placeholders so the
+scatter / replicate / apply / gather flow can be watched on a machine without GPUs.
+"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from torch.utils.data import DataLoader
+
+import pytorch_distributed_training_tutorials_b200 as b2
+from pytorch_distributed_training_tutorials_b200.models.toy import SampleModel
+
+input_size, output_size, batch_size, data_size = 32, 2, 32, 1024
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--devices", default=None, help="comma separated, e.g. cuda:0,cuda:1 or cpu,cpu")
+    ap.add_argument("--fused-sum", action="store_true", help="fuse the output gather with the sum loss")
+    ap.add_argument("--max-batches", type=int, default=0)
+    args = ap.parse_args()
+    if args.devices:
+        devices = args.devices.split(",")
+    else:
+        devices = [f"cuda:{i}" for i in range(torch.cuda.device_count())] or ["cpu"]
+    device = torch.device(devices[0])
+    rand_loader = DataLoader(dataset=b2.RandomDataset(input_size, data_size), batch_size=batch_size, shuffle=True)
+    model = SampleModel(input_size, output_size).to(device)
+    if len(devices) > 1:
+        print("Let's use", len(devices), "devices!")
+        model = b2.DataParallel(model, device_ids=devices)
+    optimizer = torch.optim.Adam(model.parameters(), lr=1e-3)
+    for i, data in enumerate(rand_loader):
+        optimizer.zero_grad()
+        data = data.to(device)
+        if args.fused_sum and isinstance(model, b2.DataParallel):
+            loss, output = model.forward_sum(data)
+        else:
+            output = model(data)
+            loss = output.sum()
+        print("Outside: input size", data.size(), "output_size", output.size())
+        loss.backward()
+        optimizer.step()
+        if args.max_batches and i + 1 >= args.max_batches:
+            break
