@@ -25,9 +25,8 @@ for (H, Cin, Cout, R, s, cnt) in SHAPES:
     Ho = H // s
     dy = torch.randn(NB, Ho, Ho, Cout, device=dev).bfloat16()
     gf = 2.0 * NB * Ho * Ho * Cout * Cin * R * R / 1e9
-    wt = NV.filter_transpose(w, stride=s)
     t_f = time_cuda(lambda: NV.conv2d_fprop(x, w, stride=s), iters=10)
-    t_d = time_cuda(lambda: NV.conv2d_dgrad(dy, wt, x.shape, R, stride=s), iters=10)
+    t_d = time_cuda(lambda: NV.conv2d_dgrad(dy, w, x.shape, R, stride=s), iters=10)
     t_w = time_cuda(lambda: NV.conv2d_wgrad(x, dy, R, stride=s), iters=10)
     xc = x.permute(0, 3, 1, 2); wc = w.permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last); dyc = dy.permute(0, 3, 1, 2)
     c_f = time_cuda(lambda: F.conv2d(xc, wc, stride=s, padding=R // 2), iters=10)

@@ -10,8 +10,7 @@ dev = torch.device("cuda:0")
 x = torch.randn(NB, H, H, Cin, device=dev).bfloat16()
 w = (torch.randn(Cout, R, R, Cin, device=dev) * 0.05).bfloat16()
 dy = torch.randn(NB, H // s, H // s, Cout, device=dev).bfloat16()
-wt = NV.filter_transpose(w, stride=s)
-fn = {"fprop": lambda: NV.conv2d_fprop(x, w, stride=s), "dgrad": lambda: NV.conv2d_dgrad(dy, wt, x.shape, R, stride=s),
+fn = {"fprop": lambda: NV.conv2d_fprop(x, w, stride=s), "dgrad": lambda: NV.conv2d_dgrad(dy, w, x.shape, R, stride=s),
       "wgrad": lambda: NV.conv2d_wgrad(x, dy, R, stride=s)}[what]
 for _ in range(5):
     fn()

@@ -54,6 +54,7 @@ struct GemmParams {
   int out_fp32, relu, atomic;
   int qbox[3];              // per-warp store sub-box (w, h, n): a quarter (32 rows) of the tile
   int qoff[4][3];           // origin of quarter q inside the tile box (w, h, n)
+  int b_mn;                 // kind 0 only: B operand is MN-major (dgrad reads the filter un-transposed)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   const float* bias;
 };
@@ -188,7 +189,16 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
               const uint32_t fb = full0 + stage * 8;
               mbar_expect_tx_s(fb, stage_bytes);
               tma_load_4d_s(sa, ma, fb, cb * kBK, wt, ht, n0);
-              tma_load_2d_s(sa + a_stage_bytes, &maps.b[0], fb, kcoord, nb0);
+              if (!p.b_mn) {
+                tma_load_2d_s(sa + a_stage_bytes, &maps.b[0], fb, kcoord, nb0);
+              } else {
+                // MN-major B: rows = reduction index (this 64-block of it), columns = output
+                // channels of this tile, fetched as 64-wide chunks; tp.pad = filter tap index.
+                const int col0 = tp.pad * p.n_valid + nb0;
+#pragma unroll 1
+                for (int c = 0; c < (p.BN >> 6); ++c)
+                  tma_load_2d_s(sa + a_stage_bytes + c * 8192, &maps.b[0], fb, col0 + c * 64, cb * kBK);
+              }
               if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
           }
@@ -243,10 +253,11 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      const bool mn = p.kind == 1;
-      const uint32_t idesc = umma_idesc_bf16(kBM, p.BN, mn, mn);
-      const uint32_t lbo = mn ? 8192u : 16u;
-      const uint32_t kstep = mn ? 2048u : 32u;
+      const bool a_mn = p.kind == 1;
+      const bool b_mn = p.kind == 1 || p.b_mn;
+      const uint32_t idesc = umma_idesc_bf16(kBM, p.BN, a_mn, b_mn);
+      const uint32_t lbo_a = a_mn ? 8192u : 16u, lbo_b = b_mn ? 8192u : 16u;
+      const uint32_t kstep_a = a_mn ? 2048u : 32u, kstep_b = b_mn ? 2048u : 32u;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -265,8 +276,8 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
           const uint32_t sb = sa + a_stage_bytes;
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
-            const uint64_t da = umma_desc_sw128(sa + k * kstep, lbo, 1024);
-            const uint64_t db = umma_desc_sw128(sb + k * kstep, lbo, 1024);
+            const uint64_t da = umma_desc_sw128(sa + k * kstep_a, lbo_a, 1024);
+            const uint64_t db = umma_desc_sw128(sb + k * kstep_b, lbo_b, 1024);
             umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&bars->empty[stage]);
@@ -914,39 +925,37 @@ __global__ void zero_phase_kernel(__nv_bfloat16* base, int NB, int Ho, int Wo, i
   }
 }
 
-// NHWC conv2d data gradient.  dy: [NB,Ho,Wo,Cout] bf16, dx: [NB,H,W,Cin] bf16 (fully overwritten).
-// `wt` is the per-phase transposed filter produced by b200dt_filter_transpose_bf16:
-// for every output phase (py, px) in [0,stride)^2, in that order, the taps (rr, ss) (row-major
-// order) with (py + pad - rr) % stride == 0 and (px + pad - ss) % stride == 0 are stored as
-// wt_phase[Cin][tap][Cout] = w[Cout][rr][ss][Cin].  Then
-//   dx(s*i + py, s*j + px) = sum_taps dy(i + (py + pad - rr)/s, j + (px + pad - ss)/s) * w[., rr, ss, .]
+// NHWC conv2d data gradient.  dy: [NB,Ho,Wo,Cout] bf16, w: the forward filter [Cout,R,R,Cin] bf16
+// (read in place as an MN-major B operand: no transposed copy), dx: [NB,H,W,Cin] bf16, fully
+// overwritten.  For every output phase (py, px) in [0,stride)^2 the taps (rr, ss) with
+// (py + pad - rr) % stride == 0 and (px + pad - ss) % stride == 0 contribute
+//   dx(s*i + py, s*j + px) += dy(i + (py + pad - rr)/s, j + (px + pad - ss)/s) * w[., rr, ss, .]
 // which is again a tiled-pixel implicit GEMM whose output rows land in a phase view of dx.
-extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx, int NB, int H,
+extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, int H,
                                         int W, int Cin, int Cout, int R, int stride,
                                         void* stream) {
-  if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cout % 64) || (Cin % 8)) return -3;
+  if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cout % 8) || (Cin % 8)) return -3;
   if (stride == 2 && ((H | W) & 1)) return -3;
   const int Ho = H / stride, Wo = W / stride;
-  const __nv_bfloat16* wtb = reinterpret_cast<const __nv_bfloat16*>(wt);
   const int pad = R / 2;
-  long long wt_off = 0;
   for (int py = 0; py < stride; ++py)
     for (int px = 0; px < stride; ++px) {
       GemmParams p{};
       p.kind = 0;
+      p.b_mn = 1;
       p.BN = pick_bn(Cin);
       pick_box(Wo, Ho, 128, &p.bw, &p.bh, &p.bn);
       p.tiles_w = Wo / p.bw; p.tiles_h = Ho / p.bh;
       p.tiles_m = p.tiles_w * p.tiles_h * ((NB + p.bn - 1) / p.bn);
       p.tiles_n = (Cin + p.BN - 1) / p.BN;
       p.splits = 1;
-      p.cin_blocks = Cout / 64;
+      p.cin_blocks = (Cout + 63) / 64;
       int nt = 0;
       for (int rr = 0; rr < R; ++rr)
         for (int ss = 0; ss < R; ++ss) {
           const int ey = py + pad - rr, ex = px + pad - ss;
           if ((ey % stride) || (ex % stride)) continue;
-          p.taps[nt++] = Tap{0, (int8_t)(ex / stride), (int8_t)(ey / stride), 0};
+          p.taps[nt++] = Tap{0, (int8_t)(ex / stride), (int8_t)(ey / stride), (int8_t)(rr * R + ss)};
         }
       p.ntaps = nt;
       __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx) + ((long long)py * W + px) * Cin;
@@ -971,7 +980,8 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx
       int r = make_map4(&ma[0], dy, dims, str, box);
       if (r) return r;
       ma[1] = ma[2] = ma[3] = ma[0];
-      r = make_map2(&mb[0], wtb + wt_off, (long long)nt * Cout, Cin, (long long)nt * Cout, kBK, p.BN);
+      // B = w viewed as [Cout rows][R*R*Cin columns]; a chunk is 64 columns x 64 rows
+      r = make_map2(&mb[0], w, (long long)R * R * Cin, Cout, (long long)R * R * Cin, 64, 64);
       if (r) return r;
       mb[1] = mb[2] = mb[3] = mb[0];
       CUtensorMap mc;
@@ -985,9 +995,54 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx
       }
       r = launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
       if (r) return r;
-      wt_off += (long long)nt * Cout * Cin;
     }
   return (int)cudaGetLastError();
+}
+
+// C[M,N] (bf16 or fp32) = A[M,K] * B[K,N]; A and B row-major bf16 (B is consumed as an MN-major
+// operand).  Linear dgrad: dX[M,in] = dY[M,out] * W[out,in] without transposing W.
+extern "C" int b200dt_gemm_nn_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                                   int lda, int ldb, int ldc, int out_fp32, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((lda % 8) || (ldb % 8)) return -3;
+  GemmParams p{};
+  p.kind = 0;
+  p.b_mn = 1;
+  p.BN = pick_bn(N);
+  p.tiles_m = (M + kBM - 1) / kBM;
+  p.tiles_n = (N + p.BN - 1) / p.BN;
+  p.splits = 1;
+  p.kb_total = (K + kBK - 1) / kBK;
+  p.kb_per_split = p.kb_total;
+  p.bw = 128; p.bh = 1; p.bn = 1;
+  p.tiles_w = p.tiles_m; p.tiles_h = 1;
+  p.W = M; p.H = 1; p.NB = 1;
+  p.cin_blocks = p.kb_total;
+  p.ntaps = 1;
+  p.taps[0] = Tap{0, 0, 0, 0};
+  p.C = C; p.sN = 0; p.sH = 0; p.sW = ldc;
+  p.n_valid = N; p.m_valid = M;
+  p.out_fp32 = out_fp32; p.relu = 0; p.atomic = 0; p.bias = nullptr;
+  CUtensorMap ma[kMaxMaps], mb[kMaxMaps];
+  long long dims[4] = {K, M, 1, 1};
+  long long str[3] = {lda, (long long)lda * M, (long long)lda * M};
+  int box[4] = {kBK, 128, 1, 1};
+  int r = make_map4(&ma[0], A, dims, str, box);
+  if (r) return r;
+  ma[1] = ma[2] = ma[3] = ma[0];
+  r = make_map2(&mb[0], B, N, K, ldb, 64, 64);
+  if (r) return r;
+  mb[1] = mb[2] = mb[3] = mb[0];
+  CUtensorMap mc;
+  long long dimsC[4] = {N, M, 1, 1};
+  long long strC[3] = {ldc, (long long)ldc * M, (long long)ldc * M};
+  const bool tma_out = out_map_ok(C, strC, out_fp32 != 0) && quarter_box(p);
+  if (tma_out) {
+    int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
+    r = make_map_out(&mc, C, dimsC, strC, qb, out_fp32 != 0);
+    if (r) return r;
+  }
+  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
 
 // Filter re-layout for the data gradient (see b200dt_conv2d_dgrad_bf16). w: [Cout,R,R,Cin] bf16,

@@ -25,6 +25,9 @@ extern "C" {
 /* C[M,N] = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU); A, B bf16 row-major, C bf16 or fp32. */
 int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
                         int ldb, int ldc, const float* bias, int relu, int out_fp32, void* stream);
+/* C[M,N] = A[M,K] * B[K,N]; row-major bf16 inputs (Linear dgrad without a transposed weight). */
+int b200dt_gemm_nn_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                        int ldc, int out_fp32, void* stream);
 /* C[M,N] fp32 = A[Kr,M]^T * B[Kr,N] (weight gradients). splits = 0: library picks and clears C. */
 int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C, int M, int N, int Kr,
                                int lda, int ldb, int ldc, int splits, void* stream);
@@ -33,7 +36,8 @@ int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, int NB, int 
                              int Cout, int R, int stride, int relu, void* stream);
 int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int NB, int H, int W,
                              int Cin, int Cout, int R, int stride, void* stream);
-int b200dt_conv2d_dgrad_bf16(const void* dy, const void* wt, void* dx, int NB, int H, int W,
+/* dgrad reads the forward filter w [Cout,R,R,Cin] in place (MN-major B operand). */
+int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, int H, int W,
                              int Cin, int Cout, int R, int stride, void* stream);
 int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R, int stride,
                                  void* stream);

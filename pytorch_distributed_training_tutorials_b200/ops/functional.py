@@ -57,9 +57,9 @@ class _Linear(torch.autograd.Function):
         dyb = dy2.to(BF16).contiguous()
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            wt = NV.transpose_bf16(_shadow(weight))            # [K, N]: K-major operand for dgrad
             if N % 8 == 0:
-                dx = NV.gemm_tn(dyb, wt).view(ctx.x_shape).to(ctx.x_dtype)
+                # W [out, in] is consumed in place as the MN-major B operand: no transposed copy
+                dx = NV.gemm_nn(dyb, _shadow(weight)).view(ctx.x_shape).to(ctx.x_dtype)
             else:
                 dx = (dy2.float() @ weight.detach()).view(ctx.x_shape).to(ctx.x_dtype)
         if ctx.needs_input_grad[1]:
@@ -93,8 +93,7 @@ class _Conv2d(torch.autograd.Function):
         dy = dy.contiguous()
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            wt = NV.filter_transpose(_shadow(weight), stride=ctx.stride)
-            dx = NV.conv2d_dgrad(dy, wt, x.shape, R, stride=ctx.stride)
+            dx = NV.conv2d_dgrad(dy, _shadow(weight), x.shape, R, stride=ctx.stride)
         if ctx.needs_input_grad[1]:
             dw = NV.conv2d_wgrad(x, dy, R, stride=ctx.stride)
         return dx, dw, None

@@ -43,6 +43,20 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     return out
 
 
+def gemm_nn(a: torch.Tensor, b: torch.Tensor, out_dtype=BF16) -> torch.Tensor:
+    """``a[M,K] @ b[K,N]`` with both operands row-major (b is read as an MN-major tcgen05 operand)."""
+    _need(a, BF16, "a"); _need(b, BF16, "b")
+    M, K = a.shape
+    K2, N = b.shape
+    if K != K2 or K % 8 or N % 8:
+        raise ValueError("gemm_nn: K mismatch or K/N % 8 != 0")
+    out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    with on_device(a.device):
+        check(lib().b200dt_gemm_nn_bf16(ptr(a), ptr(b), ptr(out), M, N, K, K, N, out.stride(0),
+                                        int(out_dtype == F32), stream_ptr(a.device)), "gemm_nn")
+    return out
+
+
 def gemm_nt_reduce(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``a[R,M]^T @ b[R,N]`` -> fp32 ``[M,N]`` (weight gradients; reduction over rows)."""
     _need(a, BF16, "a"); _need(b, BF16, "b")
@@ -93,13 +107,14 @@ def filter_transpose(w: torch.Tensor, stride: int = 1) -> torch.Tensor:
     return wt
 
 
-def conv2d_dgrad(dy: torch.Tensor, wt: torch.Tensor, x_shape, R: int, stride: int = 1) -> torch.Tensor:
-    _need(dy, BF16, "dy"); _need(wt, BF16, "wt")
+def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape, R: int, stride: int = 1) -> torch.Tensor:
+    """Data gradient; ``w`` is the forward filter ``[Cout, R, R, Cin]`` (no transposed copy needed)."""
+    _need(dy, BF16, "dy"); _need(w, BF16, "w")
     NB, H, W, Cin = x_shape
     Cout = dy.shape[-1]
     dx = torch.empty((NB, H, W, Cin), device=dy.device, dtype=BF16)
     with on_device(dy.device):
-        check(lib().b200dt_conv2d_dgrad_bf16(ptr(dy), ptr(wt), ptr(dx), NB, H, W, Cin, Cout, R, stride,
+        check(lib().b200dt_conv2d_dgrad_bf16(ptr(dy), ptr(w), ptr(dx), NB, H, W, Cin, Cout, R, stride,
                                              stream_ptr(dy.device)), "conv2d_dgrad")
     return dx
 

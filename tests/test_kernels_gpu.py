@@ -35,6 +35,15 @@ def test_gemm_tn(M, N, K):
     assert rel_err(out2, torch.relu(ref + bias)) < 2e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (2048, 4096, 4096), (300, 72, 200), (16, 2048, 1000), (1000, 1000, 2048)])
+def test_gemm_nn(M, N, K):
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=dev()).bfloat16()
+    b = torch.randn(K, N, device=dev()).bfloat16()
+    out = NV.gemm_nn(a, b, out_dtype=torch.float32)
+    assert rel_err(out, a.float() @ b.float()) < 2e-3
+
+
 @pytest.mark.parametrize("R,M,N", [(64, 64, 64), (4096, 128, 128), (1000, 1000, 2048), (777, 72, 200),
                                    (100000, 64, 64), (32768, 256, 64)])
 def test_gemm_nt_reduce(R, M, N):
@@ -86,8 +95,7 @@ def test_conv_dgrad_wgrad(cfg):
     yref.backward(dy.float().permute(0, 3, 1, 2))
     dw = NV.conv2d_wgrad(x, dy, R, stride=s)
     assert rel_err(dw, wr.grad.permute(0, 2, 3, 1)) < 5e-3
-    wt = NV.filter_transpose(w, stride=s)
-    dx = NV.conv2d_dgrad(dy, wt, x.shape, R, stride=s)
+    dx = NV.conv2d_dgrad(dy, w, x.shape, R, stride=s)
     assert rel_err(dx, nhwc(xr.grad)) < 1e-2
 
 
