@@ -13,7 +13,9 @@
 namespace b200 {
 
 constexpr int kBnThreads = 256;
-constexpr int kUnroll = 4;       // independent 16-byte loads in flight per thread and stream
+constexpr int kUnroll = 4;
+constexpr int kUnrollBwd = 4;
+constexpr int kRep = B200DT_BN_REPLICAS;   // copies of the partial-sum array: spreads the atomics of ~900 CTAs       // independent 16-byte loads in flight per thread and stream
 
 struct Slab {
   int cols_per_block;   // vector (8-channel) columns handled by one CTA
@@ -67,7 +69,25 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
     if (col >= cv) continue;
     float s = 0.f;
     for (int w = 0; w < nwarps; ++w) s += smem[(w * NV + v) * cols + x];
-    atomicAdd(out + (v >> 3) * C + col * 8 + (v & 7), s);
+    atomicAdd(out + (size_t)(blockIdx.y % kRep) * 2 * C + (v >> 3) * C + col * 8 + (v & 7), s);
+  }
+  // The last CTA to finish folds the replicas into copy 0, so consumers read one plain array.
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(out + (size_t)kRep * 2 * C);
+    is_last = (atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < kRep; ++r) t += *reinterpret_cast<volatile float*>(out + (size_t)r * 2 * C + i);
+      out[i] = t;
+    }
   }
 }
 
@@ -104,6 +124,13 @@ bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long
     }
   }
   fold_and_add<2>(acc, tx, cols, C, smem, sums);
+}
+
+__device__ __forceinline__ float rep_sum(const float* __restrict__ sums, int C, int idx) {
+  float s = 0.f;
+#pragma unroll
+  for (int r = 0; r < kRep; ++r) s += sums[(size_t)r * 2 * C + idx];
+  return s;
 }
 
 template <bool kTrain>
@@ -179,10 +206,13 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
   }
 }
 
+// kMask: 0 = no ReLU, 1 = mask from the saved output y, 2 = mask recomputed from x
+template <int kMask>
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                      const uint4* __restrict__ x, const float* __restrict__ save_mean,
-                     const float* __restrict__ save_invstd, float* __restrict__ sums,
+                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ sums,
                      uint4* __restrict__ dres, long long rows, int C, int relu, int cols,
                      int rowlanes) {
   extern __shared__ float smem[];
@@ -190,35 +220,43 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
   float acc[2][8];
-  float mean[8], invstd[8];
+  float mean[8], invstd[8], fscale[8], fshift[8];
+  // y == nullptr with relu: the ReLU mask is recomputed from x with the forward's arithmetic
+  // (y = x * scale + shift), which saves reading y (only valid without a residual input)
+  constexpr bool remask = (kMask == 2);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     acc[0][j] = acc[1][j] = 0.f;
     const int c = (col < cv ? col : 0) * 8 + j;
     mean[j] = save_mean[c];
     invstd[j] = save_invstd[c];
+    fscale[j] = remask ? gamma[c] * invstd[j] : 0.f;
+    fshift[j] = remask ? beta[c] - mean[j] * fscale[j] : 0.f;
   }
   if (col < cv) {
     const long long stride = (long long)gridDim.y * rowlanes;
-    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnroll * stride) {
-      uint4 vg[kUnroll], vx[kUnroll], vy[kUnroll];
+    for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnrollBwd * stride) {
+      uint4 vg[kUnrollBwd], vx[kUnrollBwd], vy[kUnrollBwd];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < kUnrollBwd; ++u) {
         const long long rr = r + u * stride;
         if (rr < rows) {
           vg[u] = ld_nc_v4(dy + rr * cv + col);
           vx[u] = ld_nc_v4(x + rr * cv + col);
-          if (relu) vy[u] = ld_nc_v4(y + rr * cv + col);
+          if (kMask == 1) vy[u] = ld_nc_v4(y + rr * cv + col);
         }
       }
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < kUnrollBwd; ++u) {
         const long long rr = r + u * stride;
         if (rr >= rows) break;
         float g[8], xv[8];
         unpack8(vg[u], g);
         unpack8(vx[u], xv);
-        if (relu) {
+        if (remask) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = (xv[j] * fscale[j] + fshift[j]) > 0.f ? g[j] : 0.f;
+        } else if (kMask == 1) {
           float yv[8];
           unpack8(vy[u], yv);
 #pragma unroll
@@ -236,51 +274,59 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
   fold_and_add<2>(acc, tx, cols, C, smem, sums);
 }
 
+template <int kMask>
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                     const uint4* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ sums, uint4* __restrict__ dx, float* dgamma,
-                    float* dbeta, long long rows, int C, int relu, int cols, int rowlanes) {
+                    const float* __restrict__ beta, const float* __restrict__ sums,
+                    uint4* __restrict__ dx, float* dgamma, float* dbeta, long long rows, int C,
+                    int relu, int cols, int rowlanes) {
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
   if (col >= cv) return;
-  float mean[8], invstd[8], scale[8], mg[8], mgx[8];
+  float mean[8], invstd[8], scale[8], mg[8], mgx[8], fshift[8];
   const float inv_rows = 1.f / (float)rows;
+  constexpr bool remask = (kMask == 2);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = col * 8 + j;
     mean[j] = save_mean[c];
     invstd[j] = save_invstd[c];
     scale[j] = gamma[c] * invstd[j];
-    mg[j] = sums[c] * inv_rows;
-    mgx[j] = sums[C + c] * inv_rows;
+    fshift[j] = remask ? beta[c] - mean[j] * scale[j] : 0.f;
+    const float sg = sums[c], sgx = sums[C + c];
+    mg[j] = sg * inv_rows;
+    mgx[j] = sgx * inv_rows;
     if (blockIdx.y == 0 && ty == 0) {
-      if (dbeta != nullptr) dbeta[c] = sums[c];
-      if (dgamma != nullptr) dgamma[c] = sums[C + c];
+      if (dbeta != nullptr) dbeta[c] = sg;
+      if (dgamma != nullptr) dgamma[c] = sgx;
     }
   }
   const long long stride = (long long)gridDim.y * rowlanes;
-  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnroll * stride) {
-    uint4 vg[kUnroll], vx[kUnroll], vy[kUnroll];
+  for (long long r = (long long)blockIdx.y * rowlanes + ty; r < rows; r += kUnrollBwd * stride) {
+    uint4 vg[kUnrollBwd], vx[kUnrollBwd], vy[kUnrollBwd];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kUnrollBwd; ++u) {
       const long long rr = r + u * stride;
       if (rr < rows) {
         vg[u] = ld_nc_v4(dy + rr * cv + col);
         vx[u] = ld_nc_v4(x + rr * cv + col);
-        if (relu) vy[u] = ld_nc_v4(y + rr * cv + col);
+        if (kMask == 1) vy[u] = ld_nc_v4(y + rr * cv + col);
       }
     }
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kUnrollBwd; ++u) {
       const long long rr = r + u * stride;
       if (rr >= rows) break;
       float g[8], xv[8];
       unpack8(vg[u], g);
       unpack8(vx[u], xv);
-      if (relu) {
+      if (remask) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = (xv[j] * scale[j] + fshift[j]) > 0.f ? g[j] : 0.f;
+      } else if (kMask == 1) {
         float yv[8];
         unpack8(vy[u], yv);
 #pragma unroll
@@ -305,7 +351,7 @@ using namespace b200;
 extern "C" int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * (2 * C * kRep + 1), st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
@@ -343,30 +389,42 @@ extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y
 }
 
 extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x,
-                                    const float* save_mean, const float* save_invstd, float* sums,
-                                    void* dres, long long rows, int C, int relu, void* stream) {
+                                    const float* save_mean, const float* save_invstd,
+                                    const float* gamma, const float* beta, float* sums, void* dres,
+                                    long long rows, int C, int relu, void* stream) {
   if (C % 8 || rows <= 0) return -3;
+  if (relu && y == nullptr && (gamma == nullptr || beta == nullptr)) return -3;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * (2 * C * kRep + 1), st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
-  bn_bwd_reduce_kernel<<<s.grid, kBnThreads, smem, st>>>(
-      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
-      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, sums,
-      reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter);
+  const int mask = !relu ? 0 : (y != nullptr ? 1 : 2);
+#define B200_LAUNCH_REDUCE(M)                                                                      \
+  bn_bwd_reduce_kernel<M><<<s.grid, kBnThreads, smem, st>>>(                                       \
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
+      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
+      reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter)
+  if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1); else B200_LAUNCH_REDUCE(2);
+#undef B200_LAUNCH_REDUCE
   return (int)cudaGetLastError();
 }
 
 extern "C" int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x,
                                    const float* save_mean, const float* save_invstd,
-                                   const float* gamma, const float* sums, void* dx, float* dgamma,
-                                   float* dbeta, long long rows, int C, int relu, void* stream) {
+                                   const float* gamma, const float* beta, const float* sums,
+                                   void* dx, float* dgamma, float* dbeta, long long rows, int C,
+                                   int relu, void* stream) {
   if (C % 8 || rows <= 0) return -3;
+  if (relu && y == nullptr && beta == nullptr) return -3;
   Slab s = make_slab(rows, C, target_blocks());
-  bn_bwd_apply_kernel<<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
-      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, sums,
-      reinterpret_cast<uint4*>(dx), dgamma, dbeta, rows, C, relu, s.cols_per_block, s.rows_per_iter);
+  const int mask = !relu ? 0 : (y != nullptr ? 1 : 2);
+#define B200_LAUNCH_APPLY(M)                                                                       \
+  bn_bwd_apply_kernel<M><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(                         \
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
+      reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
+      reinterpret_cast<uint4*>(dx), dgamma, dbeta, rows, C, relu, s.cols_per_block, s.rows_per_iter)
+  if (mask == 0) B200_LAUNCH_APPLY(0); else if (mask == 1) B200_LAUNCH_APPLY(1); else B200_LAUNCH_APPLY(2);
+#undef B200_LAUNCH_APPLY
   return (int)cudaGetLastError();
 }

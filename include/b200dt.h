@@ -55,7 +55,10 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
  * Replaces cuDNN BatchNorm + ATen relu/add in torchvision Bottleneck (03.model_parallel.ipynb:810).
  * csrc/bn.cu.  x, y, residual, dy, dx, dres: [rows, C] bf16 (NHWC flattened); C % 8 == 0. */
 
-/* sums[0..C) = sum x, sums[C..2C) = sum x^2 (fp32, cleared by the call). */
+/* `sums` holds B200DT_BN_REPLICAS copies of {sum x [C], sum x^2 [C]} (fp32; cleared by the call; CTAs
+ * spread their atomics over the copies and the last CTA folds them into copy 0, which is what the
+ * apply kernels read) followed by one ticket word: 2*C*B200DT_BN_REPLICAS + 1 floats. */
+#define B200DT_BN_REPLICAS 16
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
 /* y = act(gamma * (x - mean) * invstd + beta (+ residual)); writes mean/invstd (fp32 [C] each)
  * and updates running stats with `momentum` (unbiased variance), all from `sums`. */
@@ -69,13 +72,15 @@ int b200dt_bn_apply_eval(const void* x, const void* residual, void* y, const flo
                          int C, float eps, int relu, void* stream);
 /* Backward phase 1: g = dy * (y > 0 if relu); sums[0..C) = sum g, sums[C..2C) = sum g * xhat;
  * optionally writes g to dres (gradient of the residual branch). */
+/* With relu != 0 and y == NULL the mask is recomputed from x, gamma, beta (no residual case). */
 int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x, const float* save_mean,
-                         const float* save_invstd, float* sums, void* dres, long long rows, int C,
-                         int relu, void* stream);
+                         const float* save_invstd, const float* gamma, const float* beta, float* sums,
+                         void* dres, long long rows, int C, int relu, void* stream);
 /* Backward phase 2: dx = gamma*invstd*(g - sum_g/rows - xhat*sum_gx/rows); dgamma, dbeta fp32. */
 int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x, const float* save_mean,
-                        const float* save_invstd, const float* gamma, const float* sums, void* dx,
-                        float* dgamma, float* dbeta, long long rows, int C, int relu, void* stream);
+                        const float* save_invstd, const float* gamma, const float* beta,
+                        const float* sums, void* dx, float* dgamma, float* dbeta, long long rows, int C,
+                        int relu, void* stream);
 
 /* ---------------------------------------------------------------- pooling (csrc/pool.cu)
  * Replaces nn.MaxPool2d(3,2,1) / AdaptiveAvgPool2d(1) (03.model_parallel.ipynb:815,824). */

@@ -55,8 +55,8 @@ _SIGS = {
     "b200dt_bn_stats": [vp, vp, i64, i32, vp],
     "b200dt_bn_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp],
     "b200dt_bn_apply_eval": [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp],
-    "b200dt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
-    "b200dt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
+    "b200dt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
+    "b200dt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
     "b200dt_maxpool3x3s2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
     "b200dt_maxpool3x3s2_bwd": [vp, vp, vp, i32, i32, i32, i32, vp],
     "b200dt_avgpool_fwd": [vp, vp, i32, i32, i32, vp],

@@ -150,7 +150,9 @@ class _BatchNorm(torch.autograd.Function):
             y = NV.bn_apply_eval(x2, r2, gamma.detach(), beta.detach(), running_mean, running_var, eps, relu)
             mean = running_mean
             invstd = torch.rsqrt(running_var + eps)
-        ctx.save_for_backward(x2, y, gamma, mean, invstd)
+        # without a residual input the ReLU mask can be recomputed from x in backward: y is not kept
+        keep_y = relu and residual is not None
+        ctx.save_for_backward(x2, y if keep_y else None, gamma, beta, mean, invstd)
         ctx.relu = relu
         ctx.has_res = residual is not None
         ctx.shape = shp
@@ -159,13 +161,14 @@ class _BatchNorm(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y, gamma, mean, invstd = ctx.saved_tensors
+        x2, y, gamma, beta, mean, invstd = ctx.saved_tensors
         Cc = ctx.shape[-1]
         dy2 = dy.reshape(-1, Cc).contiguous()
         if not ctx.training:
             raise RuntimeError("backward through eval-mode BatchNorm is not supported")
         want_res = ctx.has_res and ctx.needs_input_grad[3]
-        dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res)
+        dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res,
+                                                 beta=beta.detach())
         return (dx.view(ctx.shape), dgamma, dbeta, dres.view(ctx.shape) if dres is not None else None,
                 None, None, None, None, None, None)
 

@@ -15,6 +15,7 @@ from .._lib import check, lib, on_device, ptr, stream_ptr
 
 BF16 = torch.bfloat16
 F32 = torch.float32
+BN_REPLICAS = 16          # B200DT_BN_REPLICAS in include/b200dt.h
 
 
 def _need(t: torch.Tensor, dtype, name: str) -> None:
@@ -165,7 +166,7 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------- batch norm
 def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
     rows, Cc = x2d.shape
-    sums = torch.empty(2 * Cc, device=x2d.device, dtype=F32)
+    sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=x2d.device, dtype=F32)
     with on_device(x2d.device):
         check(lib().b200dt_bn_stats(ptr(x2d), ptr(sums), rows, Cc, stream_ptr(x2d.device)), "bn_stats")
     return sums
@@ -193,11 +194,12 @@ def bn_apply_eval(x2d, residual, gamma, beta, mean, var, eps, relu) -> torch.Ten
     return y
 
 
-def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_dres: bool):
-    """Returns (dx, dgamma, dbeta, dres or None)."""
+def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_dres: bool, beta=None):
+    """Returns (dx, dgamma, dbeta, dres or None). With ``relu`` and ``y2d is None`` the ReLU mask is
+    recomputed from ``x2d`` (needs ``beta``; only valid when the forward had no residual input)."""
     rows, Cc = x2d.shape
     dev = x2d.device
-    sums = torch.empty(2 * Cc, device=dev, dtype=F32)
+    sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=dev, dtype=F32)
     dres = torch.empty_like(dy2d) if want_dres else None
     dx = torch.empty_like(x2d)
     dgamma = torch.empty(Cc, device=dev, dtype=F32)
@@ -205,15 +207,16 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
     with on_device(dev):
         st = stream_ptr(dev)
         check(lib().b200dt_bn_bwd_reduce(ptr(dy2d), ptr(y2d), ptr(x2d), ptr(save_mean), ptr(save_invstd),
-                                         ptr(sums), ptr(dres), rows, Cc, int(relu), st), "bn_bwd_reduce")
+                                         ptr(gamma), ptr(beta), ptr(sums), ptr(dres), rows, Cc, int(relu), st),
+              "bn_bwd_reduce")
         if want_dres:   # masked gradient already materialised: reuse it, skip the y read
             check(lib().b200dt_bn_bwd_apply(ptr(dres), None, ptr(x2d), ptr(save_mean), ptr(save_invstd),
-                                            ptr(gamma), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta), rows, Cc,
-                                            0, st), "bn_bwd_apply")
+                                            ptr(gamma), ptr(beta), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta),
+                                            rows, Cc, 0, st), "bn_bwd_apply")
         else:
             check(lib().b200dt_bn_bwd_apply(ptr(dy2d), ptr(y2d), ptr(x2d), ptr(save_mean), ptr(save_invstd),
-                                            ptr(gamma), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta), rows, Cc,
-                                            int(relu), st), "bn_bwd_apply")
+                                            ptr(gamma), ptr(beta), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta),
+                                            rows, Cc, int(relu), st), "bn_bwd_apply")
     return dx, dgamma, dbeta, dres
 
 

@@ -142,7 +142,7 @@ def test_batchnorm(rows, C, relu, res):
     if relu:
         y2 = torch.relu(y2)
     y2.backward(dy.float())
-    dx, dgamma, dbeta, dres = NV.bn_backward(dy, y, x, mean, invstd, g, relu, res)
+    dx, dgamma, dbeta, dres = NV.bn_backward(dy, y if res else None, x, mean, invstd, g, relu, res, beta=b)
     # the relu mask is taken from the bf16 output, so allow a little slack
     assert rel_err(dx, xr.grad) < 3e-2
     assert rel_err(dgamma, gref.grad) < 2e-2
