@@ -27,6 +27,7 @@ constexpr int kBK = 64;           // K elements per stage (one 128-byte swizzle 
 constexpr int kThreads = 320;          // 2 control warps + 8 epilogue warps
 constexpr int kMaxTaps = 9;
 constexpr int kMaxMaps = 4;
+constexpr int kColAccBytes = 2 * 256 * 4;      // fused BN statistics: {sum, sumsq}[256] of the current tile
 constexpr int kStageOutBytes = 128 * 128;   // 8 epilogue warps x (32 rows x 128 B); x2 = budget kept for staging
 
 struct Tap {
@@ -54,6 +55,8 @@ struct GemmParams {
   int out_fp32, relu, atomic;
   int qbox[3];              // per-warp store sub-box (w, h, n): a quarter (32 rows) of the tile
   int qoff[4][3];           // origin of quarter q inside the tile box (w, h, n)
+  float* bn_sums;           // optional: fused BatchNorm statistics of the bf16 output (see bn.cu layout)
+  int bn_C;                 // channels of that BN (== n_valid)
   int b_mn;                 // kind 0 only: B operand is MN-major (dgrad reads the filter un-transposed)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   const float* bias;
@@ -119,14 +122,16 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const float (&f
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // 1024-byte alignment is required by the 128-byte swizzle atoms.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // 1024-byte alignment is required by the 128-byte swizzle atoms; the kernel has no static
+  // shared memory, so the dynamic window starts at the (aligned) base of the CTA's shared space.
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int a_stage_bytes = kBM * kBK * 2;            // 16 KB
   const int b_stage_bytes = p.BN * kBK * 2;           // 8..32 KB
   const int stage_bytes = a_stage_bytes + b_stage_bytes;
   uint8_t* stage_out = smem + p.stages * stage_bytes;          // 2 x 16 KB epilogue staging
-  Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes);
+  float* col_acc = reinterpret_cast<float*>(stage_out + 2 * kStageOutBytes);     // [2][256]
+  Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes + kColAccBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -149,6 +154,8 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   if (warp == 1) {
     tmem_alloc<512>(&bars->tmem_base);
   }
+  if (p.bn_sums != nullptr)
+    for (int i = threadIdx.x; i < kColAccBytes / 4; i += blockDim.x) col_acc[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -406,6 +413,23 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
           }
           fence_proxy_async();             // generic-proxy smem writes -> visible to TMA
           __syncwarp();
+          if (p.bn_sums != nullptr && !p.out_fp32) {
+            // Fused BatchNorm statistics: lane l owns columns 2l, 2l+1 of this 64-column slab and
+            // adds up this warp's 32 rows straight from the staged (already bf16-rounded) tile;
+            // rows outside the tensor hold exact zeros (TMA zero fill), so they do not count.
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            const uint8_t* colp = buf + ((lane & 3) << 2);
+#pragma unroll 8
+            for (int r = 0; r < 32; ++r) {
+              const uint32_t u = *reinterpret_cast<const uint32_t*>(colp + r * 128 + (((lane >> 2) ^ (r & 7)) << 4));
+              const float2 f = unpack_bf16x2(u);
+              s0 += f.x; s1 += f.y; q0 += f.x * f.x; q1 += f.y * f.y;
+            }
+            float* accb = col_acc;
+            const int cc = sl * 64 + lane * 2;
+            atomicAdd(accb + cc, s0); atomicAdd(accb + cc + 1, s1);
+            atomicAdd(accb + 256 + cc, q0); atomicAdd(accb + 256 + cc + 1, q1);
+          }
           if (lane == 0) {
             if (p.atomic)
               asm volatile(
@@ -460,9 +484,50 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+      if (p.bn_sums != nullptr) {
+        // all eight epilogue warps have added their rows of this tile: flush the tile's column
+        // sums to global memory (spread over the replicas) and clear the buffer for tile t + 2
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        float* accb = col_acc;
+        float* dstb = p.bn_sums + (size_t)(blockIdx.x % B200DT_BN_REPLICAS) * 2 * p.bn_C;
+        const int e = (warp - 2) * 32 + lane;          // 0..255: one column per thread
+        if (e < p.BN) {
+          const int c = col_base + e;
+          const float sv = accb[e], qv = accb[256 + e];
+          accb[e] = 0.f; accb[256 + e] = 0.f;
+          if (c < p.n_valid) { atomicAdd(dstb + c, sv); atomicAdd(dstb + p.bn_C + c, qv); }
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");      // cleared before the next tile adds
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (p.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (p.bn_sums != nullptr) {
+      // the last CTA to get here folds the replicas into copy 0 (what bn_apply reads)
+      __threadfence();
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      uint32_t mine = 0, fold_last = 0;
+      if (threadIdx.x == 64) {
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.bn_sums + (size_t)B200DT_BN_REPLICAS * 2 * p.bn_C);
+        mine = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      }
+      // broadcast the verdict through the barrier's OR-reduction (no static shared memory: the
+      // kernel asks for the full 227 KB as dynamic shared memory)
+      asm volatile(
+          "{\n.reg .pred pin, pout;\nsetp.ne.u32 pin, %1, 0;\n"
+          "bar.red.or.pred pout, 2, 256, pin;\nselp.u32 %0, 1, 0, pout;\n}\n"
+          : "=r"(fold_last) : "r"(mine) : "memory");
+      if (fold_last) {
+        __threadfence();
+        for (int i = threadIdx.x - 64; i < 2 * p.bn_C; i += 256) {
+          float tsum = 0.f;
+#pragma unroll
+          for (int r = 0; r < B200DT_BN_REPLICAS; ++r)
+            tsum += *reinterpret_cast<volatile float*>(p.bn_sums + (size_t)r * 2 * p.bn_C + i);
+          p.bn_sums[i] = tsum;
+        }
+      }
+    }
   }
 
   tc_fence_before();
@@ -568,7 +633,7 @@ static int num_sms() {
 static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
                   const CUtensorMap* mapC, GemmParams& p, cudaStream_t stream) {
   const int stage_bytes = kBM * kBK * 2 + p.BN * kBK * 2;
-  const int fixed = 2 * kStageOutBytes + (int)sizeof(Barriers) + 1024;
+  const int fixed = 2 * kStageOutBytes + kColAccBytes + (int)sizeof(Barriers) + 64;
   int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return -2;
@@ -648,12 +713,18 @@ static void pick_box(int W, int H, int target, int* bw, int* bh, int* bn) {
 using namespace b200;
 
 // C[M,N] (bf16 or fp32) = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU)     -- all row-major, bf16 inputs.
+static int clear_bn_sums(float* bn_sums, int C, cudaStream_t st) {
+  if (bn_sums == nullptr) return 0;
+  return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * B200DT_BN_REPLICAS + 1), st);
+}
+
 extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                                    int lda, int ldb, int ldc, const float* bias, int relu,
-                                   int out_fp32, void* stream) {
+                                   int out_fp32, float* bn_sums, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if ((lda % 8) || (ldb % 8) || (K % 8)) return -3;
   GemmParams p{};
+  p.bn_sums = bn_sums; p.bn_C = N;
   p.kind = 0;
   p.BN = pick_bn(N);
   p.tiles_m = (M + kBM - 1) / kBM;
@@ -687,6 +758,11 @@ extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M,
   if (tma_out) {
     int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
     r = make_map_out(&mc, C, dimsC, strC, qb, out_fp32 != 0);
+    if (r) return r;
+  }
+  if (bn_sums != nullptr) {
+    if (!tma_out || out_fp32) return -3;        // fused statistics live in the TMA-store epilogue
+    r = clear_bn_sums(bn_sums, N, (cudaStream_t)stream);
     if (r) return r;
   }
   return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
@@ -759,7 +835,7 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
 // Cin % 64 == 0.  For stride 2, H and W must be even.
 extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, int NB, int H, int W,
                                         int Cin, int Cout, int R, int stride, int relu,
-                                        void* stream) {
+                                        float* bn_sums, void* stream) {
   if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cin % 64) || (Cout % 8)) return -3;
   if (stride == 2 && ((H | W) & 1)) return -3;
   const int Ho = H / stride, Wo = W / stride;
@@ -824,6 +900,12 @@ extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, i
   if (tma_out) {
     int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
     r = make_map_out(&mc, y, dimsC, strC, qb, false);
+    if (r) return r;
+  }
+  if (bn_sums != nullptr) {
+    if (!tma_out || relu) return -3;            // statistics are those of the raw conv output
+    p.bn_sums = bn_sums; p.bn_C = Cout;
+    r = clear_bn_sums(bn_sums, Cout, (cudaStream_t)stream);
     if (r) return r;
   }
   return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);

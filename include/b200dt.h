@@ -22,9 +22,12 @@ extern "C" {
  * Replaces nn.Linear (ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)
  * and the ResNet-50 convolutions (03.model_parallel.ipynb:807-833). csrc/gemm.cu */
 
-/* C[M,N] = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU); A, B bf16 row-major, C bf16 or fp32. */
+/* C[M,N] = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU); A, B bf16 row-major, C bf16 or fp32.
+ * bn_sums (optional, bf16 output only): per-column sum / sum of squares of C accumulated in the
+ * epilogue, in the layout b200dt_bn_apply reads (2*N*B200DT_BN_REPLICAS + 1 floats, see below). */
 int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
-                        int ldb, int ldc, const float* bias, int relu, int out_fp32, void* stream);
+                        int ldb, int ldc, const float* bias, int relu, int out_fp32, float* bn_sums,
+                        void* stream);
 /* C[M,N] = A[M,K] * B[K,N]; row-major bf16 inputs (Linear dgrad without a transposed weight). */
 int b200dt_gemm_nn_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                         int ldc, int out_fp32, void* stream);
@@ -33,7 +36,7 @@ int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C, int M, in
                                int lda, int ldb, int ldc, int splits, void* stream);
 /* NHWC conv2d, square filter R in {1,3}, pad R/2, stride in {1,2}, Cin % 64 == 0. */
 int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, int NB, int H, int W, int Cin,
-                             int Cout, int R, int stride, int relu, void* stream);
+                             int Cout, int R, int stride, int relu, float* bn_sums, void* stream);
 int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int NB, int H, int W,
                              int Cin, int Cout, int R, int stride, void* stream);
 /* dgrad reads the forward filter w [Cout,R,R,Cin] in place (MN-major B operand). */

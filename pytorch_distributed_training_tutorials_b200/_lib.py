@@ -41,10 +41,10 @@ class _Counted:
 vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint64
 
 _SIGS = {
-    "b200dt_gemm_tn_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp],
+    "b200dt_gemm_tn_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp, vp],
     "b200dt_gemm_nn_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_gemm_nt_reduce_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
-    "b200dt_conv2d_fprop_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "b200dt_conv2d_fprop_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp],
     "b200dt_conv2d_wgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_conv2d_dgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_filter_transpose_bf16": [vp, vp, i32, i32, i32, i32, vp],

@@ -35,10 +35,18 @@ class Bottleneck(nn.Module):
             )
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x))
-        out = self.bn2(self.conv2(out))
-        return self.bn3(self.conv3(out), residual=identity)
+        t = self.training            # in training the convs emit the BN statistics from their epilogue
+        if self.downsample is None:
+            identity = x
+        else:
+            d = self.downsample[0](x, with_stats=t)
+            identity = self.downsample[1](d[0], sums=d[1]) if t else self.downsample[1](d)
+        o = self.conv1(x, with_stats=t)
+        out = self.bn1(o[0], sums=o[1]) if t else self.bn1(o)
+        o = self.conv2(out, with_stats=t)
+        out = self.bn2(o[0], sums=o[1]) if t else self.bn2(o)
+        o = self.conv3(out, with_stats=t)
+        return self.bn3(o[0], residual=identity, sums=o[1]) if t else self.bn3(o, residual=identity)
 
 
 class ResNet(nn.Module):
@@ -68,7 +76,11 @@ class ResNet(nn.Module):
 
     def features_stage0(self, x: torch.Tensor) -> torch.Tensor:
         """conv1 .. layer2 (the reference's ``seq1``, 03.model_parallel.ipynb:812-819)."""
-        x = self.maxpool(self.bn1(self.conv1(x)))
+        if self.training:
+            c, s = self.conv1(x, with_stats=True)
+            x = self.maxpool(self.bn1(c, sums=s))
+        else:
+            x = self.maxpool(self.bn1(self.conv1(x)))
         return self.layer2(self.layer1(x))
 
     def features_stage1(self, x: torch.Tensor) -> torch.Tensor:

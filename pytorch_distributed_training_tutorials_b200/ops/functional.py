@@ -79,15 +79,21 @@ def linear(x, weight, bias=None, relu: bool = False, out_fp32: bool = False):
 
 class _Conv2d(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, stride):
+    def forward(ctx, x, weight, stride, with_stats):
         wb = _shadow(weight)
-        y = NV.conv2d_fprop(x, wb, stride=stride)
         ctx.save_for_backward(x, weight)
         ctx.stride = stride
-        return y
+        ctx.with_stats = with_stats
+        if with_stats:
+            # per-channel sum / sum of squares of the output, accumulated in the conv epilogue
+            sums = NV.bn_sums_buffer(weight.shape[0], x.device)
+            y = NV.conv2d_fprop(x, wb, stride=stride, bn_sums=sums)
+            ctx.mark_non_differentiable(sums)
+            return y, sums
+        return NV.conv2d_fprop(x, wb, stride=stride)
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *unused):
         x, weight = ctx.saved_tensors
         R = weight.shape[1]
         dy = dy.contiguous()
@@ -96,54 +102,62 @@ class _Conv2d(torch.autograd.Function):
             dx = NV.conv2d_dgrad(dy, _shadow(weight), x.shape, R, stride=ctx.stride)
         if ctx.needs_input_grad[1]:
             dw = NV.conv2d_wgrad(x, dy, R, stride=ctx.stride)
-        return dx, dw, None
+        return dx, dw, None, None
 
 
-def conv2d(x, weight, stride: int = 1):
-    """NHWC conv, weight ``[Cout, R, R, Cin]``, R in {1,3}, pad R//2, stride in {1,2}."""
-    return _Conv2d.apply(x, weight, stride)
+def conv2d(x, weight, stride: int = 1, with_stats: bool = False):
+    """NHWC conv, weight ``[Cout, R, R, Cin]``, R in {1,3}, pad R//2, stride in {1,2}.
+    ``with_stats=True`` returns ``(y, sums)``: the BatchNorm statistics of ``y`` come out of the
+    conv epilogue for free; hand ``sums`` to ``batch_norm(..., sums=sums)``."""
+    return _Conv2d.apply(x, weight, stride, with_stats)
 
 
 class _StemConv(torch.autograd.Function):
     """7x7 stride-2 pad-3 convolution of the fp32 NCHW network input (Cin = 3)."""
 
     @staticmethod
-    def forward(ctx, x, weight):
+    def forward(ctx, x, weight, with_stats):
         NB, _, H, W = x.shape
         cols = NV.stem_im2col(x.contiguous())
         wk = torch.zeros((weight.shape[0], NV.STEM_LDK), device=x.device, dtype=BF16)
         wk[:, :147] = weight.detach().reshape(weight.shape[0], 147)
-        y = NV.gemm_tn(cols, wk)
+        sums = NV.bn_sums_buffer(weight.shape[0], x.device) if with_stats else None
+        y = NV.gemm_tn(cols, wk, bn_sums=sums)
         # the patch matrix is kept for the weight gradient (memory is cheap on a 180 GB part;
         # re-gathering it costs a full extra pass over the input)
         ctx.save_for_backward(cols, weight)
-        return y.view(NB, H // 2, W // 2, weight.shape[0])
+        y = y.view(NB, H // 2, W // 2, weight.shape[0])
+        if with_stats:
+            ctx.mark_non_differentiable(sums)
+            return y, sums
+        return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *unused):
         cols, weight = ctx.saved_tensors
         dw = None
         if ctx.needs_input_grad[1]:
             dy2 = dy.reshape(-1, weight.shape[0]).contiguous()
             dwk = NV.gemm_nt_reduce(dy2, cols)               # [64, 160]
             dw = dwk[:, :147].reshape(weight.shape).contiguous()
-        return None, dw
+        return None, dw, None
 
 
-def stem_conv(x_nchw_f32, weight):
+def stem_conv(x_nchw_f32, weight, with_stats: bool = False):
     """weight ``[64, 7, 7, 3]`` (OHWI)."""
-    return _StemConv.apply(x_nchw_f32, weight)
+    return _StemConv.apply(x_nchw_f32, weight, with_stats)
 
 
 class _BatchNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training, sums):
         shp = x.shape
         Cc = shp[-1]
         x2 = x.reshape(-1, Cc)
         r2 = residual.reshape(-1, Cc) if residual is not None else None
         if training:
-            sums = NV.bn_stats(x2)
+            if sums is None:
+                sums = NV.bn_stats(x2)
             y, mean, invstd = NV.bn_apply(x2, r2, sums, gamma.detach(), beta.detach(), running_mean,
                                           running_var, eps, momentum, relu)
         else:
@@ -170,13 +184,15 @@ class _BatchNorm(torch.autograd.Function):
         dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res,
                                                  beta=beta.detach())
         return (dx.view(ctx.shape), dgamma, dbeta, dres.view(ctx.shape) if dres is not None else None,
-                None, None, None, None, None, None)
+                None, None, None, None, None, None, None)
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, residual=None, eps: float = 1e-5,
-               momentum: float = 0.1, relu: bool = False, training: bool = True):
-    """y = act(BN(x) + residual) with batch statistics; updates running stats in place."""
-    return _BatchNorm.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training)
+               momentum: float = 0.1, relu: bool = False, training: bool = True, sums=None):
+    """y = act(BN(x) + residual) with batch statistics; updates running stats in place.
+    ``sums``: statistics already produced by the conv that wrote ``x`` (skips the stats pass)."""
+    return _BatchNorm.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training,
+                            sums)
 
 
 class _MaxPool(torch.autograd.Function):

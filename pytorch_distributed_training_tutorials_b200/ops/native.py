@@ -25,9 +25,15 @@ def _need(t: torch.Tensor, dtype, name: str) -> None:
 
 
 # --------------------------------------------------------------------------- GEMM / conv
+def bn_sums_buffer(C: int, device) -> torch.Tensor:
+    """Scratch for BatchNorm statistics: replicated {sum, sum of squares} + ticket (see bn.cu)."""
+    return torch.empty(2 * C * BN_REPLICAS + 1, device=device, dtype=F32)
+
+
 def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
-            out_dtype=BF16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """``a[M,K] @ b[N,K]^T (+bias) (relu)``; bf16 inputs, fp32 accumulation on tcgen05."""
+            out_dtype=BF16, out: Optional[torch.Tensor] = None, bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``a[M,K] @ b[N,K]^T (+bias) (relu)``; bf16 inputs, fp32 accumulation on tcgen05.
+    ``bn_sums``: optional buffer from ``bn_sums_buffer`` that receives the column statistics of the output."""
     _need(a, BF16, "a"); _need(b, BF16, "b")
     M, K = a.shape
     N, K2 = b.shape
@@ -39,7 +45,7 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
         _need(bias, F32, "bias")
     with on_device(a.device):
         check(lib().b200dt_gemm_tn_bf16(ptr(a), ptr(b), ptr(out), M, N, K, K, K, out.stride(0),
-                                        ptr(bias), int(relu), int(out.dtype == F32),
+                                        ptr(bias), int(relu), int(out.dtype == F32), ptr(bn_sums),
                                         stream_ptr(a.device)), "gemm_tn")
     return out
 
@@ -73,7 +79,8 @@ def gemm_nt_reduce(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor]
     return out
 
 
-def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool = False) -> torch.Tensor:
+def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool = False,
+                 bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
     _need(x, BF16, "x"); _need(w, BF16, "w")
     NB, H, W, Cin = x.shape
     Cout, R, S, Cin2 = w.shape
@@ -81,7 +88,7 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool =
     y = torch.empty((NB, H // stride, W // stride, Cout), device=x.device, dtype=BF16)
     with on_device(x.device):
         check(lib().b200dt_conv2d_fprop_bf16(ptr(x), ptr(w), ptr(y), NB, H, W, Cin, Cout, R, stride,
-                                             int(relu), stream_ptr(x.device)), "conv2d_fprop")
+                                             int(relu), ptr(bn_sums), stream_ptr(x.device)), "conv2d_fprop")
     return y
 
 

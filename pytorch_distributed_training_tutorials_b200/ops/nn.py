@@ -59,8 +59,9 @@ class Conv2d(nn.Module):
         self._register_state_dict_hook(_export_oihw)
         self._register_load_state_dict_pre_hook(_import_oihw, with_module=True)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return Fn.conv2d(x, self.weight, self.stride)
+    def forward(self, x: torch.Tensor, with_stats: bool = False):
+        """``with_stats=True`` -> ``(y, sums)`` for a following ``BatchNorm2d(y, sums=sums)``."""
+        return Fn.conv2d(x, self.weight, self.stride, with_stats)
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
@@ -78,8 +79,8 @@ class StemConv(nn.Module):
         self._register_state_dict_hook(_export_oihw)
         self._register_load_state_dict_pre_hook(_import_oihw, with_module=True)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return Fn.stem_conv(x, self.weight)
+    def forward(self, x: torch.Tensor, with_stats: bool = False):
+        return Fn.stem_conv(x, self.weight, with_stats)
 
 
 def _export_oihw(module, state_dict, prefix, local_metadata):
@@ -108,11 +109,12 @@ class BatchNorm2d(nn.Module):
         self.register_buffer("running_var", torch.ones(num_features))
         self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
 
-    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None,
+                sums: Optional[torch.Tensor] = None) -> torch.Tensor:
         if self.training:
             self.num_batches_tracked += 1
         return Fn.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, residual,
-                             self.eps, self.momentum, self.relu, self.training)
+                             self.eps, self.momentum, self.relu, self.training, sums)
 
     def extra_repr(self) -> str:
         return f"{self.num_features}, eps={self.eps}, momentum={self.momentum}, relu={self.relu}"

@@ -99,6 +99,21 @@ def test_conv_dgrad_wgrad(cfg):
     assert rel_err(dx, nhwc(xr.grad)) < 1e-2
 
 
+@pytest.mark.parametrize("cfg", [(8, 56, 56, 64, 256, 1, 1), (32, 14, 14, 256, 256, 3, 1), (5, 28, 28, 128, 128, 3, 2), (130, 7, 7, 2048, 512, 1, 1)])
+def test_conv_fused_bn_statistics(cfg):
+    NB, H, W, Cin, Cout, R, s = cfg
+    torch.manual_seed(7)
+    x = torch.randn(NB, H, W, Cin, device=dev()).bfloat16()
+    w = (torch.randn(Cout, R, R, Cin, device=dev()) / (R * Cin ** 0.5)).bfloat16()
+    sums = NV.bn_sums_buffer(Cout, dev())
+    y = NV.conv2d_fprop(x, w, stride=s, bn_sums=sums)
+    ref = NV.bn_stats(y.view(-1, Cout))
+    yf = y.float().view(-1, Cout)
+    assert torch.allclose(sums[:Cout], yf.sum(0), rtol=2e-3, atol=2e-2 * yf.abs().sum(0).max().item() / yf.shape[0] ** 0.5 + 1e-2)
+    assert torch.allclose(sums[:2 * Cout], ref[:2 * Cout], rtol=2e-3, atol=1.0)
+    assert rel_err(sums[Cout:2 * Cout], (yf * yf).sum(0)) < 2e-3
+
+
 def test_stem_im2col_conv():
     torch.manual_seed(3)
     x = torch.randn(4, 3, 64, 64, device=dev())
