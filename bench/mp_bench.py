@@ -69,6 +69,50 @@ def reference_cells():
     return ns
 
 
+def gpu_bound(res):
+    """Second workload: the same models with batch 1024 at 224x224 and inputs already on the GPU, so a
+    micro-batch of 256 keeps a B200 busy for longer than the host needs to issue it (the notebook's
+    120 x 128^2 batches are bound by the host-side randn() and launch overhead on this hardware)."""
+    from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50, PipelineParallelResNet50
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD
+    B, S, steps = 1024, 224, 3
+    x = torch.randn(B, 3, S, S, device="cuda:0")
+    lab = torch.zeros(B, num_classes).scatter_(1, torch.randint(0, num_classes, (B, 1)), 1)
+
+    def run(model, opt, out_dev, loss):
+        y = lab.to(out_dev)
+        def f():
+            for _ in range(steps):
+                opt.zero_grad()
+                loss(model(x), y).backward()
+                opt.step()
+        r = timed(f, repeats=5)
+        r["img_per_s"] = steps * B / (r["device_ms_mean"] / 1e3)
+        return r
+    m = resnet50(num_classes=num_classes).to("cuda:0"); o = FusedSGD(m.parameters(), lr=1e-3)
+    res["gpu_bound/ours_single_gpu"] = run(m, o, "cuda:0", Fn.mse_loss); del m, o
+    if torch.cuda.device_count() >= 2:
+        m = ModelParallelResNet50(num_classes=num_classes); o = FusedSGD(m.parameters(), lr=1e-3)
+        res["gpu_bound/ours_naive_mp"] = run(m, o, "cuda:1", Fn.mse_loss); del m, o
+        for cut in ("layer2", "layer1"):
+            for split in (128, 256, 512):
+                m = PipelineParallelResNet50(split_size=split, num_classes=num_classes, split_after=cut); o = FusedSGD(m.parameters(), lr=1e-3)
+                res[f"gpu_bound/ours_pipelined_mp_cut_{cut}_split{split}"] = run(m, o, "cuda:1", Fn.mse_loss); del m, o
+        m = ModelParallelResNet50(num_classes=num_classes, split_after="layer1"); o = FusedSGD(m.parameters(), lr=1e-3)
+        res["gpu_bound/ours_naive_mp_cut_layer1"] = run(m, o, "cuda:1", Fn.mse_loss); del m, o
+    ns = reference_cells()
+    if ns is not None:
+        import torchvision.models as models
+        mse = nn.MSELoss()
+        rn = models.resnet50(num_classes=num_classes).to("cuda:0"); ro = optim.SGD(rn.parameters(), lr=1e-3)
+        res["gpu_bound/reference_single_gpu_fp32"] = run(rn, ro, "cuda:0", mse); del rn, ro
+        if torch.cuda.device_count() >= 2:
+            mp = ns["ModelParallelResNet50"](); ro = optim.SGD(mp.parameters(), lr=1e-3)
+            res["gpu_bound/reference_naive_mp_fp32"] = run(mp, ro, "cuda:1", mse); del mp, ro
+
+
 def main():
     from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
     from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50, PipelineParallelResNet50
@@ -94,6 +138,7 @@ def main():
         if torch.cuda.device_count() >= 2:
             mp = ns["ModelParallelResNet50"]()
             res["reference_naive_mp"] = timed(lambda: ns["train"](mp))
+    gpu_bound(res)
     print("| variant | device ms / train() (mean +- std) | host s (timeit-style) | img/s |\n|---|---|---|---|")
     for k, v in res.items():
         print(f"| {k} | {v['device_ms_mean']:.1f} +- {v['device_ms_std']:.1f} | {v['host_s_mean']:.3f} | {v['img_per_s']:.0f} |")

@@ -74,18 +74,32 @@ class ResNet(nn.Module):
         mods += [Bottleneck(self.inplanes, planes) for _ in range(1, blocks)]
         return nn.Sequential(*mods)
 
+    SEGMENTS = ("stem", "layer1", "layer2", "layer3", "layer4", "pool")
+
+    def run_segment(self, name: str, x: torch.Tensor) -> torch.Tensor:
+        if name == "stem":
+            if self.training:
+                c, s = self.conv1(x, with_stats=True)
+                return self.maxpool(self.bn1(c, sums=s))
+            return self.maxpool(self.bn1(self.conv1(x)))
+        if name == "pool":
+            return self.avgpool(x)
+        return getattr(self, name)(x)
+
+    def run_segments(self, x: torch.Tensor, first: str, last: str) -> torch.Tensor:
+        """Run the consecutive segments ``first .. last`` (inclusive) of SEGMENTS."""
+        i, j = self.SEGMENTS.index(first), self.SEGMENTS.index(last)
+        for name in self.SEGMENTS[i:j + 1]:
+            x = self.run_segment(name, x)
+        return x
+
     def features_stage0(self, x: torch.Tensor) -> torch.Tensor:
         """conv1 .. layer2 (the reference's ``seq1``, 03.model_parallel.ipynb:812-819)."""
-        if self.training:
-            c, s = self.conv1(x, with_stats=True)
-            x = self.maxpool(self.bn1(c, sums=s))
-        else:
-            x = self.maxpool(self.bn1(self.conv1(x)))
-        return self.layer2(self.layer1(x))
+        return self.run_segments(x, "stem", "layer2")
 
     def features_stage1(self, x: torch.Tensor) -> torch.Tensor:
         """layer3 .. avgpool (the reference's ``seq2``, 03.model_parallel.ipynb:821-825)."""
-        return self.avgpool(self.layer4(self.layer3(x)))
+        return self.run_segments(x, "layer3", "pool")
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """x: ``[N, 3, H, W]`` fp32 (NCHW, like torchvision) -> logits ``[N, num_classes]`` fp32."""
