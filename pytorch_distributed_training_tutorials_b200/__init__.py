@@ -20,6 +20,8 @@ __version__ = "0.1.0"
 _LAZY = {
     "DistributedDataParallel": ("parallel.ddp", "DistributedDataParallel"),
     "DataParallel": ("parallel.data_parallel", "DataParallel"),
+    "GraphedPipeline": ("parallel.graphed_pipeline", "GraphedPipeline"),
+    "PipelineStage": ("parallel.pipeline", "PipelineStage"),
     "Trainer": ("trainer", "Trainer"),
     "save_checkpoint": ("checkpoint", "save_checkpoint"),
     "load_checkpoint": ("checkpoint", "load_checkpoint"),

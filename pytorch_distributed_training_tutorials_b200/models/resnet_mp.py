@@ -61,3 +61,11 @@ class PipelineParallelResNet50(ModelParallelResNet50):
             prev = cur
         outs.append(self.stage1(prev))
         return torch.cat(outs, dim=0)
+
+    def graphed(self, loss_fn, example_x: torch.Tensor, example_y: torch.Tensor):
+        """CUDA-graph replayed training step for this split (``parallel.graphed_pipeline``): the
+        micro-batch count is ``batch // split_size``; returns an object with ``train_step(x, y)``."""
+        from ..parallel.graphed_pipeline import GraphedPipeline
+        chunks = max(1, example_x.shape[0] // self.split_size)
+        return GraphedPipeline([self.stage0, self.stage1], [self.dev0, self.dev1], chunks, loss_fn,
+                               example_x, example_y, parameters=list(self.parameters()))

@@ -1,0 +1,98 @@
+"""CUDA-graph replayed pipeline (parallel/graphed_pipeline.py) against the eager micro-batched schedule.
+Runs with both stages on one GPU when only one is visible (the schedule and the graphs are the same)."""
+import copy
+
+import pytest
+import torch
+from torch import nn
+
+pytestmark = pytest.mark.gpu
+
+
+def _devs():
+    return ["cuda:0", "cuda:1"] if torch.cuda.device_count() >= 2 else ["cuda:0", "cuda:0"]
+
+
+def _eager_step(stages, devs, x, y, loss_fn, chunks):
+    total = 0.0
+    for xi, yi in zip(x.chunk(chunks), y.chunk(chunks)):
+        a = xi
+        for st, d in zip(stages, devs):
+            a = st(a.to(d))
+        li = loss_fn(a, yi.to(devs[-1])) / chunks
+        li.backward()
+        total = total + li.detach()
+    return total
+
+
+def test_graphed_pipeline_mlp_matches_eager_over_steps():
+    import pytorch_distributed_training_tutorials_b200 as b2
+    from pytorch_distributed_training_tutorials_b200.ops import nn as bnn, functional as Fn
+    devs = _devs()
+    torch.manual_seed(0)
+    s0 = nn.Sequential(bnn.Linear(64, 256, relu=True), bnn.Linear(256, 128, relu=True)).to(devs[0])
+    s1 = nn.Sequential(bnn.Linear(128, 64, relu=True), bnn.Linear(64, 32)).to(devs[1])
+    r0, r1 = copy.deepcopy(s0), copy.deepcopy(s1)
+    x = torch.randn(256, 64, device=devs[0]); y = torch.randn(256, 32, device=devs[1])
+    pipe = b2.GraphedPipeline([s0, s1], devs, 4, Fn.mse_loss, x, y)
+    assert pipe.launches_per_step == 16
+    o = b2.FusedSGD(list(s0.parameters()) + list(s1.parameters()), lr=0.05)
+    ro = b2.FusedSGD(list(r0.parameters()) + list(r1.parameters()), lr=0.05)
+    losses, ref = [], []
+    for it in range(6):
+        torch.manual_seed(100 + it)
+        xb = torch.randn(256, 64, device=devs[0]); yb = torch.randn(256, 32, device=devs[1])
+        # alternate the two ways of clearing gradients: the flat buffers must be re-attached
+        if it % 2:
+            o.zero_grad(set_to_none=True)
+        else:
+            pipe.zero_grad()
+        losses.append(float(pipe.train_step(xb, yb)))
+        o.step()
+        ro.zero_grad(set_to_none=True)
+        ref.append(float(_eager_step([r0, r1], devs, xb, yb, Fn.mse_loss, 4)))
+        ro.step()
+    assert ref[-1] < ref[0]
+    for a, b in zip(losses, ref):
+        assert abs(a - b) <= 2e-3 * abs(b) + 1e-5, (losses, ref)
+    for p, q in zip(list(s0.parameters()) + list(s1.parameters()), list(r0.parameters()) + list(r1.parameters())):
+        assert torch.allclose(p, q, rtol=1e-3, atol=1e-4)
+
+
+def _cos(a, b):
+    a, b = a.flatten().double(), b.flatten().double()
+    return float(torch.dot(a, b) / (a.norm() * b.norm() + 1e-30))
+
+
+def test_graphed_pipeline_resnet50_matches_eager():
+    from pytorch_distributed_training_tutorials_b200.models.resnet_mp import PipelineParallelResNet50
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    devs = _devs()
+    torch.manual_seed(0)
+    m = PipelineParallelResNet50(split_size=8, num_classes=16, dev0=devs[0], dev1=devs[1], split_after="layer1")
+    r, r2 = copy.deepcopy(m), copy.deepcopy(m)
+    x = torch.randn(16, 3, 128, 128, device=devs[0]); y = torch.randint(0, 16, (16,), device=devs[1])
+    pipe = m.graphed(Fn.cross_entropy, x, y)
+    assert pipe.chunks == 2
+    # capture must not have disturbed the BatchNorm running statistics or left gradients behind
+    for (k, a), (_, b) in zip(m.state_dict().items(), r.state_dict().items()):
+        assert torch.equal(a, b), k
+    assert all(float(p.grad.abs().sum()) == 0.0 for p in m.parameters())
+    loss = pipe.train_step(x, y)
+    ref = _eager_step([r.stage0, r.stage1], devs, x, y, Fn.cross_entropy, 2)
+    ref2 = _eager_step([r2.stage0, r2.stage1], devs, x, y, Fn.cross_entropy, 2)
+    # a randomly initialised 50-layer net amplifies the fp32 atomics' ordering noise: the yardstick is how
+    # well two EAGER runs of the same kernels agree with each other
+    noise = abs(float(ref2) - float(ref))
+    assert abs(float(loss) - float(ref)) <= 3 * noise + 2e-2 * abs(float(ref))
+    cg = [_cos(p.grad, q.grad) for p, q in zip(m.parameters(), r.parameters())]
+    ce = [_cos(p.grad, q.grad) for p, q in zip(r2.parameters(), r.parameters())]
+    assert sum(cg) / len(cg) >= sum(ce) / len(ce) - 0.05, (sum(cg) / len(cg), sum(ce) / len(ce))
+    assert _cos(m.fc.weight.grad, r.fc.weight.grad) > 0.97
+    # boundary activations of every slot are the eager ones
+    for i, xi in enumerate(x.chunk(2)):
+        assert _cos(pipe.out[0][i], r2.stage0(xi).detach()) > 0.999
+    assert torch.allclose(m.bn1.running_mean, r.bn1.running_mean, atol=1e-3)
+    assert int(m.bn1.num_batches_tracked) == int(r.bn1.num_batches_tracked) == 2
+    with pytest.raises(ValueError):
+        pipe.train_step(x[:8], y[:8])
