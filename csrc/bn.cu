@@ -140,10 +140,12 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
                 const float* __restrict__ beta, float* running_mean, float* running_var,
                 float* save_mean, float* save_invstd, const float* __restrict__ in_mean,
                 const float* __restrict__ in_var, long long rows, int C, float eps, float momentum,
-                int relu, int cols, int rowlanes) {
+                int relu, int cols, int rowlanes, long long* batches_tracked) {
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
+  if (kTrain && batches_tracked != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0)
+    *batches_tracked += 1;   // nn.BatchNorm's num_batches_tracked, without a launch of its own
   if (col >= cv) return;
   float scale[8], shift[8];
   const float inv_rows = 1.f / (float)rows;
@@ -364,14 +366,14 @@ extern "C" int b200dt_bn_apply(const void* x, const void* residual, void* y, con
                                const float* gamma, const float* beta, float* running_mean,
                                float* running_var, float* save_mean, float* save_invstd,
                                long long rows, int C, float eps, float momentum, int relu,
-                               void* stream) {
+                               long long* batches_tracked, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   Slab s = make_slab(rows, C, target_blocks());
   bn_apply_kernel<true><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), sums, gamma, beta, running_mean, running_var, save_mean,
       save_invstd, nullptr, nullptr, rows, C, eps, momentum, relu, s.cols_per_block,
-      s.rows_per_iter);
+      s.rows_per_iter, batches_tracked);
   return (int)cudaGetLastError();
 }
 
@@ -384,7 +386,7 @@ extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y
   bn_apply_kernel<false><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), nullptr, gamma, beta, nullptr, nullptr, nullptr, nullptr, mean,
-      var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter);
+      var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter, nullptr);
   return (int)cudaGetLastError();
 }
 

@@ -1013,9 +1013,10 @@ __global__ void zero_phase_kernel(__nv_bfloat16* base, int NB, int Ho, int Wo, i
 // (py + pad - rr) % stride == 0 and (px + pad - ss) % stride == 0 contribute
 //   dx(s*i + py, s*j + px) += dy(i + (py + pad - rr)/s, j + (px + pad - ss)/s) * w[., rr, ss, .]
 // which is again a tiled-pixel implicit GEMM whose output rows land in a phase view of dx.
-extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, int H,
-                                        int W, int Cin, int Cout, int R, int stride,
-                                        void* stream) {
+// accumulate != 0: dx already holds a gradient of the same tensor (the residual branch) and the
+// epilogue adds to it with TMA reduce-add instead of storing, so no separate add kernel runs.
+static int conv2d_dgrad_impl(const void* dy, const void* w, void* dx, int NB, int H, int W, int Cin,
+                             int Cout, int R, int stride, int accumulate, void* stream) {
   if (!(R == 1 || R == 3) || !(stride == 1 || stride == 2) || (Cout % 8) || (Cin % 8)) return -3;
   if (stride == 2 && ((H | W) & 1)) return -3;
   const int Ho = H / stride, Wo = W / stride;
@@ -1045,8 +1046,9 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx,
       p.C = dxp;
       p.sW = (long long)stride * Cin; p.sH = (long long)stride * W * Cin;
       p.sN = (long long)H * W * Cin;
-      p.n_valid = Cin; p.out_fp32 = 0; p.relu = 0; p.atomic = 0; p.bias = nullptr;
+      p.n_valid = Cin; p.out_fp32 = 0; p.relu = 0; p.atomic = accumulate ? 1 : 0; p.bias = nullptr;
       if (nt == 0) {
+        if (accumulate) continue;          // nothing to add to this phase
         const long long total = (long long)NB * Ho * Wo * (Cin / 8);
         int blocks = (int)((total + 255) / 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
@@ -1070,6 +1072,7 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx,
       long long dimsC[4] = {Cin, Wo, Ho, NB};
       long long strC[3] = {p.sW, p.sH, p.sN};
       const bool tma_out = out_map_ok(dxp, strC, false) && quarter_box(p);
+      if (accumulate && !tma_out) return -4;    // caller falls back to dgrad + add
       if (tma_out) {
         int qb[4] = {0, p.qbox[0], p.qbox[1], p.qbox[2]};
         r = make_map_out(&mc, dxp, dimsC, strC, qb, false);
@@ -1079,6 +1082,18 @@ extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx,
       if (r) return r;
     }
   return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, int H,
+                                        int W, int Cin, int Cout, int R, int stride,
+                                        void* stream) {
+  return conv2d_dgrad_impl(dy, w, dx, NB, H, W, Cin, Cout, R, stride, 0, stream);
+}
+
+extern "C" int b200dt_conv2d_dgrad_acc_bf16(const void* dy, const void* w, void* dx, int NB, int H,
+                                            int W, int Cin, int Cout, int R, int stride,
+                                            void* stream) {
+  return conv2d_dgrad_impl(dy, w, dx, NB, H, W, Cin, Cout, R, stride, 1, stream);
 }
 
 // C[M,N] (bf16 or fp32) = A[M,K] * B[K,N]; A and B row-major bf16 (B is consumed as an MN-major

@@ -42,6 +42,11 @@ int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int NB, i
 /* dgrad reads the forward filter w [Cout,R,R,Cin] in place (MN-major B operand). */
 int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, int H, int W,
                              int Cin, int Cout, int R, int stride, void* stream);
+/* dx += dgrad(dy, w): the epilogue adds to what dx holds (TMA reduce-add, bf16), e.g. the gradient
+ * that reached the same tensor through a residual connection. Returns -4 when the output cannot be
+ * written through a tensor map (caller then uses the plain entry point and adds). */
+int b200dt_conv2d_dgrad_acc_bf16(const void* dy, const void* w, void* dx, int NB, int H, int W,
+                                 int Cin, int Cout, int R, int stride, void* stream);
 int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R, int stride,
                                  void* stream);
 
@@ -64,11 +69,12 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
 #define B200DT_BN_REPLICAS 16
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
 /* y = act(gamma * (x - mean) * invstd + beta (+ residual)); writes mean/invstd (fp32 [C] each)
- * and updates running stats with `momentum` (unbiased variance), all from `sums`. */
+ * and updates running stats with `momentum` (unbiased variance), all from `sums`.
+ * batches_tracked (optional, device int64): incremented by one, like nn.BatchNorm's counter. */
 int b200dt_bn_apply(const void* x, const void* residual, void* y, const float* sums,
                     const float* gamma, const float* beta, float* running_mean, float* running_var,
                     float* save_mean, float* save_invstd, long long rows, int C, float eps,
-                    float momentum, int relu, void* stream);
+                    float momentum, int relu, long long* batches_tracked, void* stream);
 /* Inference-style apply with given statistics. */
 int b200dt_bn_apply_eval(const void* x, const void* residual, void* y, const float* gamma,
                          const float* beta, const float* mean, const float* var, long long rows,

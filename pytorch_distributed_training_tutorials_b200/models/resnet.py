@@ -13,6 +13,7 @@ from typing import List, Optional
 import torch
 from torch import nn
 
+from ..ops import functional as Fn
 from ..ops import nn as bnn
 
 
@@ -36,6 +37,19 @@ class Bottleneck(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         t = self.training            # in training the convs emit the BN statistics from their epilogue
+        if t and x.is_cuda and torch.is_grad_enabled():
+            # the two gradients of x (first conv + identity / projection) are added inside the dgrad epilogue
+            if self.downsample is None:
+                c1, s1, identity = Fn.conv2d_skip(x, self.conv1.weight, 1, True)
+            else:
+                ds = self.downsample[0]
+                c1, s1, d, sd = Fn.conv2d_dual(x, self.conv1.weight, ds.weight, 1, ds.stride)
+                identity = self.downsample[1](d, sums=sd)
+            out = self.bn1(c1, sums=s1)
+            o = self.conv2(out, with_stats=True)
+            out = self.bn2(o[0], sums=o[1])
+            o = self.conv3(out, with_stats=True)
+            return self.bn3(o[0], residual=identity, sums=o[1])
         if self.downsample is None:
             identity = x
         else:

@@ -112,6 +112,84 @@ def conv2d(x, weight, stride: int = 1, with_stats: bool = False):
     return _Conv2d.apply(x, weight, stride, with_stats)
 
 
+class _ConvSkip(torch.autograd.Function):
+    """``(conv(x, w), x)``: the convolution that opens a residual block together with the block's
+    identity branch, so that backward can add the two gradients of ``x`` inside the dgrad epilogue
+    (TMA reduce-add into the incoming skip gradient) instead of leaving a separate add to autograd."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride, with_stats):
+        wb = _shadow(weight)
+        ctx.save_for_backward(x, weight)
+        ctx.stride = stride
+        if with_stats:
+            sums = NV.bn_sums_buffer(weight.shape[0], x.device)
+            y = NV.conv2d_fprop(x, wb, stride=stride, bn_sums=sums)
+            ctx.mark_non_differentiable(sums)
+            return y, sums, x
+        return NV.conv2d_fprop(x, wb, stride=stride), None, x
+
+    @staticmethod
+    def backward(ctx, dy, _dsums, dskip):
+        x, weight = ctx.saved_tensors
+        R = weight.shape[1]
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            if dy is None:
+                dx = dskip
+            else:
+                acc = dskip.contiguous() if dskip is not None else None
+                dx = NV.conv2d_dgrad(dy.contiguous(), _shadow(weight), x.shape, R, stride=ctx.stride,
+                                     accumulate_into=acc)
+        if ctx.needs_input_grad[1] and dy is not None:
+            dw = NV.conv2d_wgrad(x, dy.contiguous(), R, stride=ctx.stride)
+        return dx, dw, None, None
+
+
+def conv2d_skip(x, weight, stride: int = 1, with_stats: bool = False):
+    """Returns ``(y, sums or None, skip)`` with ``skip`` an alias of ``x`` for the residual branch.
+    The gradient that comes back through ``skip`` is consumed IN PLACE (it must not be shared; the
+    fused BatchNorm backward hands out a fresh tensor, which is what the models here rely on)."""
+    return _ConvSkip.apply(x, weight, stride, with_stats)
+
+
+class _ConvDual(torch.autograd.Function):
+    """Two convolutions of the same input (a block's first conv and its downsample projection):
+    backward writes the first data gradient and adds the second one in its epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, w1, w2, stride1, stride2):
+        ctx.save_for_backward(x, w1, w2)
+        ctx.strides = (stride1, stride2)
+        s1 = NV.bn_sums_buffer(w1.shape[0], x.device)
+        s2 = NV.bn_sums_buffer(w2.shape[0], x.device)
+        y1 = NV.conv2d_fprop(x, _shadow(w1), stride=stride1, bn_sums=s1)
+        y2 = NV.conv2d_fprop(x, _shadow(w2), stride=stride2, bn_sums=s2)
+        ctx.mark_non_differentiable(s1, s2)
+        return y1, s1, y2, s2
+
+    @staticmethod
+    def backward(ctx, dy1, _d1, dy2, _d2):
+        x, w1, w2 = ctx.saved_tensors
+        st1, st2 = ctx.strides
+        dy1 = dy1.contiguous()
+        dy2 = dy2.contiguous()
+        dx = dw1 = dw2 = None
+        if ctx.needs_input_grad[0]:
+            dx = NV.conv2d_dgrad(dy1, _shadow(w1), x.shape, w1.shape[1], stride=st1)
+            dx = NV.conv2d_dgrad(dy2, _shadow(w2), x.shape, w2.shape[1], stride=st2, accumulate_into=dx)
+        if ctx.needs_input_grad[1]:
+            dw1 = NV.conv2d_wgrad(x, dy1, w1.shape[1], stride=st1)
+        if ctx.needs_input_grad[2]:
+            dw2 = NV.conv2d_wgrad(x, dy2, w2.shape[1], stride=st2)
+        return dx, dw1, dw2, None, None
+
+
+def conv2d_dual(x, w1, w2, stride1: int = 1, stride2: int = 1):
+    """``(conv(x, w1), sums1, conv(x, w2), sums2)`` with one fused data gradient for ``x``."""
+    return _ConvDual.apply(x, w1, w2, stride1, stride2)
+
+
 class _StemConv(torch.autograd.Function):
     """7x7 stride-2 pad-3 convolution of the fp32 NCHW network input (Cin = 3)."""
 
@@ -150,7 +228,8 @@ def stem_conv(x_nchw_f32, weight, with_stats: bool = False):
 
 class _BatchNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training, sums):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training, sums,
+                tracked=None):
         shp = x.shape
         Cc = shp[-1]
         x2 = x.reshape(-1, Cc)
@@ -159,7 +238,7 @@ class _BatchNorm(torch.autograd.Function):
             if sums is None:
                 sums = NV.bn_stats(x2)
             y, mean, invstd = NV.bn_apply(x2, r2, sums, gamma.detach(), beta.detach(), running_mean,
-                                          running_var, eps, momentum, relu)
+                                          running_var, eps, momentum, relu, tracked)
         else:
             y = NV.bn_apply_eval(x2, r2, gamma.detach(), beta.detach(), running_mean, running_var, eps, relu)
             mean = running_mean
@@ -184,15 +263,17 @@ class _BatchNorm(torch.autograd.Function):
         dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res,
                                                  beta=beta.detach())
         return (dx.view(ctx.shape), dgamma, dbeta, dres.view(ctx.shape) if dres is not None else None,
-                None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None)
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, residual=None, eps: float = 1e-5,
-               momentum: float = 0.1, relu: bool = False, training: bool = True, sums=None):
+               momentum: float = 0.1, relu: bool = False, training: bool = True, sums=None,
+               num_batches_tracked=None):
     """y = act(BN(x) + residual) with batch statistics; updates running stats in place.
-    ``sums``: statistics already produced by the conv that wrote ``x`` (skips the stats pass)."""
+    ``sums``: statistics already produced by the conv that wrote ``x`` (skips the stats pass).
+    ``num_batches_tracked``: int64 device scalar incremented inside the apply kernel when training."""
     return _BatchNorm.apply(x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training,
-                            sums)
+                            sums, num_batches_tracked)
 
 
 class _MaxPool(torch.autograd.Function):

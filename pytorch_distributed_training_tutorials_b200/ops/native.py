@@ -115,11 +115,27 @@ def filter_transpose(w: torch.Tensor, stride: int = 1) -> torch.Tensor:
     return wt
 
 
-def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape, R: int, stride: int = 1) -> torch.Tensor:
-    """Data gradient; ``w`` is the forward filter ``[Cout, R, R, Cin]`` (no transposed copy needed)."""
+def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape, R: int, stride: int = 1,
+                 accumulate_into: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Data gradient; ``w`` is the forward filter ``[Cout, R, R, Cin]`` (no transposed copy needed).
+    ``accumulate_into``: a bf16 gradient of the same tensor that already exists (residual branch,
+    second consumer); the kernel adds to it IN PLACE in its epilogue and returns it."""
     _need(dy, BF16, "dy"); _need(w, BF16, "w")
     NB, H, W, Cin = x_shape
     Cout = dy.shape[-1]
+    if accumulate_into is not None:
+        acc = accumulate_into
+        _need(acc, BF16, "accumulate_into")
+        if tuple(acc.shape) != (NB, H, W, Cin):
+            raise ValueError("accumulate_into has the wrong shape")
+        with on_device(dy.device):
+            rc = lib().b200dt_conv2d_dgrad_acc_bf16(ptr(dy), ptr(w), ptr(acc), NB, H, W, Cin, Cout, R, stride,
+                                                    stream_ptr(dy.device))
+        if rc == 0:
+            return acc
+        if rc != -4:
+            check(rc, "conv2d_dgrad_acc")
+        return acc.add_(conv2d_dgrad(dy, w, x_shape, R, stride))     # output not expressible as a tensor map
     dx = torch.empty((NB, H, W, Cin), device=dy.device, dtype=BF16)
     with on_device(dy.device):
         check(lib().b200dt_conv2d_dgrad_bf16(ptr(dy), ptr(w), ptr(dx), NB, H, W, Cin, Cout, R, stride,
@@ -179,8 +195,11 @@ def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
     return sums
 
 
-def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, momentum, relu
-             ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, momentum, relu,
+             batches_tracked: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """``batches_tracked``: optional int64 device scalar the kernel increments (no launch of its own)."""
+    if batches_tracked is not None:
+        _need(batches_tracked, torch.int64, "batches_tracked")
     rows, Cc = x2d.shape
     y = torch.empty_like(x2d)
     save_mean = torch.empty(Cc, device=x2d.device, dtype=F32)
@@ -188,7 +207,8 @@ def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, m
     with on_device(x2d.device):
         check(lib().b200dt_bn_apply(ptr(x2d), ptr(residual), ptr(y), ptr(sums), ptr(gamma), ptr(beta),
                                     ptr(running_mean), ptr(running_var), ptr(save_mean), ptr(save_invstd),
-                                    rows, Cc, eps, momentum, int(relu), stream_ptr(x2d.device)), "bn_apply")
+                                    rows, Cc, eps, momentum, int(relu), ptr(batches_tracked),
+                                    stream_ptr(x2d.device)), "bn_apply")
     return y, save_mean, save_invstd
 
 

@@ -97,6 +97,17 @@ class _FusedBase(Optimizer):
                 cpu.append(p)
         return by_dev, cpu
 
+    def refresh_shadows(self) -> None:
+        """Re-derive the bf16 operand copies from the fp32 masters (after the masters were written by
+        something other than ``step``: a checkpoint load, a restore after warm-up iterations)."""
+        from . import native as NV
+        for group in self.param_groups:
+            for p in group["params"]:
+                sh = self._shadows.get(id(p))
+                if sh is not None and p.is_cuda and sh.device == p.device and sh.shape == p.shape:
+                    NV.cast_bf16(p.detach().contiguous(), out=sh)
+                    p._b200_shadow = (p._version, sh)
+
     def _publish_shadows(self, params) -> None:
         for p in params:
             sh = self._shadows.get(id(p))

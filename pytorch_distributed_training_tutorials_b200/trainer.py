@@ -77,15 +77,43 @@ class Trainer:
         ys = ys.to(self.device, non_blocking=True)
         return float(self._run_batch(xs, ys).item())
 
+    def run_batches(self, batches) -> list:
+        """Train on an iterable of host ``(xs, ys)`` batches, software-pipelined: the upload of batch
+        i+1 (``DevicePrefetcher``, copy stream) overlaps the kernels of batch i, and the loss of batch i
+        is copied to pinned memory on the compute stream and read on the host while batch i+1 runs.
+        Returns every step's loss as a float, in order."""
+        from .data import DevicePrefetcher
+        losses, pending = [], []
+        cuda = self.device.type == "cuda"
+        if cuda and getattr(self, "_loss_ring", None) is None:
+            self._loss_ring = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        for k, (xs, ys) in enumerate(DevicePrefetcher(batches, self.device)):
+            loss = self._run_batch(xs, ys)
+            if not cuda:
+                losses.append(float(loss))
+                continue
+            slot = self._loss_ring[k % 2]
+            slot.copy_(loss.detach().reshape(1), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            pending.append((slot, ev))
+            if len(pending) > 1:
+                s, e = pending.pop(0)
+                e.synchronize()
+                losses.append(float(s[0]))
+        for s, e in pending:
+            e.synchronize()
+            losses.append(float(s[0]))
+        return losses
+
     def _run_epoch(self, epoch: int):
         batch_size = len(next(iter(self.train_dataloader))[0])
         print(f"[GPU: {self.gpu_id} Epoch: {epoch}, Batch size: {batch_size} | Steps {len(self.train_dataloader)}]")
         sampler = getattr(self.train_dataloader, "sampler", None)
         if hasattr(sampler, "set_epoch"):
             sampler.set_epoch(epoch)
-        for xs, ys in self.train_dataloader:
-            xs = xs.to(self.device)
-            ys = ys.to(self.device)
+        from .data import DevicePrefetcher
+        for xs, ys in DevicePrefetcher(self.train_dataloader, self.device):
             self._run_batch(xs, ys)
             if self.log_every and self.global_step % self.log_every == 0:
                 from .utils.logging import log_json

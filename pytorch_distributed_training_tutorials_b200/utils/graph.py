@@ -39,8 +39,13 @@ class GraphedTrainStep:
             for m in model.modules():
                 if hasattr(m, "rebind_autograd_hooks"):
                     m.rebind_autograd_hooks()
-            for _ in range(max(warmup, 3)):      # DDP needs >= 2 eager iterations to settle its buckets
+            # the warm-up iterations (lazy kernel setup; DDP needs >= 2 to settle its buckets) must not
+            # train the model: parameters, buffers and optimizer state are put back afterwards
+            snap = self._snapshot()
+            for _ in range(max(warmup, 3)):
                 self._eager()
+            self._restore(snap)
+            del snap
         cur.wait_stream(side)
         torch.cuda.synchronize(self.device)
         self.graph = torch.cuda.CUDAGraph()
@@ -49,6 +54,20 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph):
             self.static_loss = self._eager(zero=False)
         self.kernels_per_step = _lib.launch_count - before
+
+    def _snapshot(self):
+        import copy
+        tensors = list(self.model.parameters()) + list(self.model.buffers())
+        return ([t.detach().clone() for t in tensors], tensors, copy.deepcopy(self.optimizer.state_dict()))
+
+    @torch.no_grad()
+    def _restore(self, snap) -> None:
+        saved, tensors, opt_state = snap
+        for t, s in zip(tensors, saved):
+            t.copy_(s)
+        self.optimizer.load_state_dict(opt_state)
+        if hasattr(self.optimizer, "refresh_shadows"):
+            self.optimizer.refresh_shadows()
 
     def _eager(self, zero: bool = True):
         if zero:

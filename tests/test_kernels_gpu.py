@@ -99,6 +99,49 @@ def test_conv_dgrad_wgrad(cfg):
     assert rel_err(dx, nhwc(xr.grad)) < 1e-2
 
 
+@pytest.mark.parametrize("cfg", [(8, 56, 56, 256, 64, 1, 1), (8, 56, 56, 256, 512, 1, 2), (32, 14, 14, 1024, 256, 1, 1),
+                                 (5, 28, 28, 128, 128, 3, 2), (130, 7, 7, 2048, 512, 1, 1), (32, 28, 28, 128, 128, 3, 1)])
+def test_conv_dgrad_accumulates_into_existing_gradient(cfg):
+    """dx += dgrad(dy): the residual-branch gradient is added inside the epilogue (TMA reduce-add)."""
+    NB, H, W, Cin, Cout, R, s = cfg
+    torch.manual_seed(12)
+    w = (torch.randn(Cout, R, R, Cin, device=dev()) / (R * Cin ** 0.5)).bfloat16()
+    dy = torch.randn(NB, H // s, W // s, Cout, device=dev()).bfloat16()
+    skip = torch.randn(NB, H, W, Cin, device=dev()).bfloat16()
+    plain = NV.conv2d_dgrad(dy, w, (NB, H, W, Cin), R, stride=s)
+    want = skip.float() + plain.float()
+    acc = skip.clone()
+    out = NV.conv2d_dgrad(dy, w, (NB, H, W, Cin), R, stride=s, accumulate_into=acc)
+    assert out.data_ptr() == acc.data_ptr()
+    assert rel_err(out, want) < 6e-3                 # one bf16 rounding of the sum
+
+
+def test_conv_skip_and_dual_functions_match_unfused_autograd():
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    torch.manual_seed(13)
+    x0 = torch.randn(8, 28, 28, 256, device=dev()).bfloat16()
+    w1 = (torch.randn(64, 1, 1, 256, device=dev()) / 16).requires_grad_(True)
+    w2 = (torch.randn(512, 1, 1, 256, device=dev()) / 16).requires_grad_(True)
+    for fused in (False, True):
+        x = x0.clone().requires_grad_(True)
+        if fused:
+            y, _, skip = Fn.conv2d_skip(x, w1, 1, True)
+            a, _, b, _ = Fn.conv2d_dual(x, w1, w2, 1, 2)
+        else:
+            y, skip = Fn.conv2d(x, w1), x
+            a, b = Fn.conv2d(x, w1), Fn.conv2d(x, w2, stride=2)
+        loss = (y.float() ** 2).mean() + (skip.float() * 0.37).sum() / skip.numel() + (a.float() * 0.5).mean() \
+            + (b.float() ** 2).mean()
+        loss.backward()
+        if fused:
+            got = (x.grad.clone(), w1.grad.clone(), w2.grad.clone())
+        else:
+            ref = (x.grad.clone(), w1.grad.clone(), w2.grad.clone())
+        w1.grad = None; w2.grad = None
+    for g, r in zip(got, ref):
+        assert rel_err(g, r) < 1e-2
+
+
 @pytest.mark.parametrize("cfg", [(8, 56, 56, 64, 256, 1, 1), (32, 14, 14, 256, 256, 3, 1), (5, 28, 28, 128, 128, 3, 2), (130, 7, 7, 2048, 512, 1, 1)])
 def test_conv_fused_bn_statistics(cfg):
     NB, H, W, Cin, Cout, R, s = cfg

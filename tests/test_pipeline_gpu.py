@@ -96,3 +96,35 @@ def test_graphed_pipeline_resnet50_matches_eager():
     assert int(m.bn1.num_batches_tracked) == int(r.bn1.num_batches_tracked) == 2
     with pytest.raises(ValueError):
         pipe.train_step(x[:8], y[:8])
+
+
+def test_device_prefetcher_hands_out_the_right_batches():
+    from pytorch_distributed_training_tutorials_b200.data import DevicePrefetcher
+    batches = [(torch.full((1 << 20,), float(i)).pin_memory(), torch.tensor([i]).pin_memory()) for i in range(7)]
+    sums = []
+    for x, y in DevicePrefetcher(iter(batches), "cuda:0"):
+        assert x.is_cuda and y.is_cuda
+        # a long-running consumer: the next upload lands in the other slot while this runs
+        acc = x.double()
+        for _ in range(20):
+            acc = acc * 1.0 + 0.0
+        sums.append((acc.sum() / x.numel(), y.clone()))
+    assert [round(float(s)) for s, _ in sums] == list(range(7))
+    assert [int(y) for _, y in sums] == list(range(7))
+
+
+def test_trainer_run_batches_graph_matches_step():
+    import pytorch_distributed_training_tutorials_b200 as b2
+    from pytorch_distributed_training_tutorials_b200.models.toy import MLP
+    torch.manual_seed(0)
+    m = MLP(in_features=64, hidden=128, depth=3, out_features=16)
+    r = copy.deepcopy(m)
+    in_f, out_f = 64, 16
+    batches = [(torch.randn(32, in_f).pin_memory(), torch.randint(0, out_f, (32,)).pin_memory()) for _ in range(6)]
+    t1 = b2.Trainer(m, None, b2.FusedSGD(m.parameters(), lr=0.05), gpu_id=0, wrap_ddp=False, cuda_graph=True)
+    t2 = b2.Trainer(r, None, b2.FusedSGD(r.parameters(), lr=0.05), gpu_id=0, wrap_ddp=False, cuda_graph=False)
+    got = t1.run_batches(iter(batches))
+    ref = [t2.step(x, y) for x, y in batches]
+    assert len(got) == 6
+    for a, b in zip(got, ref):
+        assert abs(a - b) <= 2e-3 * abs(b) + 1e-5, (got, ref)

@@ -241,3 +241,35 @@ def test_run_launcher_failure_and_restart(tmp_path):
     assert r.returncode == 3 and "failed with exit code 3" in r.stderr
     r = subprocess.run(base + ["--max-restarts", "1", str(script)], env=env, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "restarting worker group (1/1)" in r.stderr
+
+
+# --------------------------------------------------------------------------- prefetcher / run_batches
+def test_device_prefetcher_cpu_passthrough_and_len():
+    from pytorch_distributed_training_tutorials_b200.data import DevicePrefetcher
+    batches = [(torch.full((2, 3), float(i)), torch.tensor([i, i])) for i in range(5)]
+    pf = DevicePrefetcher(batches, "cpu")
+    assert len(pf) == 5
+    got = list(pf)
+    assert len(got) == 5
+    for i, (x, y) in enumerate(got):
+        assert torch.equal(x, batches[i][0]) and torch.equal(y, batches[i][1])
+    assert list(DevicePrefetcher([], "cpu")) == []
+
+
+def test_trainer_run_batches_cpu_matches_manual_loop():
+    import copy
+    from pytorch_distributed_training_tutorials_b200.trainer import Trainer
+    torch.manual_seed(0)
+    m = torch.nn.Linear(20, 4)
+    r = copy.deepcopy(m)
+    batches = [(torch.randn(8, 20), torch.randint(0, 4, (8,))) for _ in range(4)]
+    tr = Trainer(m, None, torch.optim.SGD(m.parameters(), lr=0.1), gpu_id=0, wrap_ddp=False)
+    losses = tr.run_batches(iter(batches))
+    opt = torch.optim.SGD(r.parameters(), lr=0.1)
+    ref = []
+    for x, y in batches:
+        opt.zero_grad(); l = torch.nn.functional.cross_entropy(r(x), y); l.backward(); opt.step(); ref.append(float(l))
+    assert losses == pytest.approx(ref, rel=1e-6)
+    assert tr.global_step == 4
+    for p, q in zip(m.parameters(), r.parameters()):
+        assert torch.allclose(p, q)
