@@ -173,7 +173,9 @@ def run_ours(args, rank, world, local):
     model = resnet50(num_classes=args.classes)
     optimizer = FusedSGD(model.parameters(), lr=1e-3)
     trainer = Trainer(model, train_dataloader=None, optimizer=optimizer, gpu_id=local, wrap_ddp=True,
-                      ddp_kwargs=dict(allreduce=args.allreduce, comm_dtype=args.comm_dtype),
+                      ddp_kwargs=dict(allreduce=args.allreduce, comm_dtype=args.comm_dtype,
+                                      max_comm_blocks=args.comm_blocks,
+                                      broadcast_buffers=not args.no_broadcast_buffers),
                       cuda_graph=not args.no_graph)
     host_x, host_y = make_host_batches(2, args.batch_size, args.image, args.classes, seed=rank)
     dev_x = [x.to(device) for x in host_x]
@@ -280,6 +282,8 @@ def main() -> None:
     ap.add_argument("--allreduce", default="auto", choices=["auto", "oneshot", "twoshot", "nvls", "nccl"])
     ap.add_argument("--comm-dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
+    ap.add_argument("--comm-blocks", type=int, default=32, help="CTAs of the fused all-reduce kernel (diagnostics)")
+    ap.add_argument("--no-broadcast-buffers", action="store_true", help="skip the per-forward buffer broadcast (diagnostics)")
     ap.add_argument("--e2e-sync", action="store_true",
                     help="end-to-end number through the synchronous Trainer.step instead of the prefetching run_batches")
     args = ap.parse_args()

@@ -65,47 +65,66 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, __nv_bfloat16* 
 }
 
 // Stem gather. Output row = (n, ho, wo); column k = (r*7 + s)*3 + c for k < 147, zero up to ldk.
-// One CTA handles one output row (n, ho): it stages the 7 x 3 input rows it needs in shared
-// memory (coalesced fp32 reads), then every thread emits 16-byte pieces of the K-major rows.
+// One CTA handles kStemRows consecutive output rows of one image: the 2*kStemRows + 5 input rows
+// they share are staged ONCE in shared memory as bf16, channel-interleaved ([row][w + 3][c], zero
+// padded), so that the 21 values of one filter row are contiguous; then thread t owns one 16-byte
+// piece (v8 = t % (ldk/8)) of the K-major output rows, keeps its eight source offsets in registers
+// and walks over the output pixels: eight 2-byte shared loads, one coalesced 16-byte store.
+constexpr int kStemRows = 4;
+
 __global__ void __launch_bounds__(256)
 stem_im2col_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ cols, int H, int W,
                    int ldk) {
-  extern __shared__ float s[];   // [7][3][W + 6]  (3 columns of zero padding on both sides)
+  extern __shared__ __align__(16) unsigned short sb[];   // [2*kStemRows + 5][(W + 6) * 3] bf16 bits
   const int Ho = H / 2, Wo = W / 2;
-  const int n = blockIdx.y, ho = blockIdx.x;
-  const int PW = W + 6;
-  for (int i = threadIdx.x; i < 7 * 3 * PW; i += blockDim.x) {
-    const int pw = i % PW;
-    const int c = (i / PW) % 3;
-    const int r = i / (PW * 3);
-    const int h = ho * 2 - 3 + r, w = pw - 3;
-    float v = 0.f;
-    if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((long long)n * 3 + c) * H + h) * W + w];
-    s[i] = v;
+  const int n = blockIdx.y, ho0 = blockIdx.x * kStemRows;
+  const int PW3 = (W + 6) * 3;
+  const int nrows = 2 * kStemRows + 5;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // zero the left / right padding columns (3 pixels x 3 channels on both sides of every row)
+  for (int i = threadIdx.x; i < nrows * 18; i += blockDim.x) {
+    const int r = i / 18, e = i % 18;
+    sb[r * PW3 + (e < 9 ? e : PW3 - 18 + e)] = 0;
   }
-  // k -> offset inside the staged rows (filter row r, channel c, filter column ss); -1 = padding
-  __shared__ short lut[256];
-  for (int k = threadIdx.x; k < 256; k += blockDim.x) {
-    short o = -1;
-    if (k < 147) {
-      const int c = k % 3, ss = (k / 3) % 7, r = k / 21;
-      o = (short)((r * 3 + c) * PW + ss);
+  // (row, channel) pairs are spread over the warps; a warp reads its W floats coalesced
+  for (int rc = warp; rc < nrows * 3; rc += 8) {
+    const int r = rc / 3, c = rc - r * 3;
+    const int h = ho0 * 2 - 3 + r;
+    unsigned short* dst = sb + r * PW3 + 9 + c;
+    if (h >= 0 && h < H) {
+      const float* src = x + (((long long)n * 3 + c) * H + h) * W;
+      for (int w = lane; w < W; w += 32)
+        dst[w * 3] = __bfloat16_as_ushort(__float2bfloat16(__ldg(src + w)));
+    } else {
+      for (int w = lane; w < W; w += 32) dst[w * 3] = 0;
     }
-    lut[k] = o;
   }
   __syncthreads();
   const int kv = ldk / 8;                       // 16-byte vectors per output row
-  __nv_bfloat16* out = cols + ((long long)n * Ho + ho) * Wo * ldk;
-  for (int i = threadIdx.x; i < Wo * kv; i += blockDim.x) {
-    const int wo = i / kv, v8 = i - wo * kv;
-    const float* base = s + wo * 2;
-    float f[8];
+  const int per_pass = blockDim.x / kv;         // output pixels per pass over the CTA
+  const int v8 = threadIdx.x % kv, slot = threadIdx.x / kv;
+  if (slot >= per_pass) return;
+  int off[8];                                   // k -> offset inside the staged rows, -1 = padding
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const short o = lut[v8 * 8 + j];
-      f[j] = o >= 0 ? base[o] : 0.f;
+  for (int j = 0; j < 8; ++j) {
+    const int k = v8 * 8 + j;
+    off[j] = k < 147 ? (k / 21) * PW3 + (k % 21) : -1;
+  }
+  const int total = kStemRows * Wo;
+  for (int q = slot; q < total; q += per_pass) {
+    const int rr = q / Wo, wo = q - rr * Wo;
+    const int ho = ho0 + rr;
+    if (ho >= Ho) break;
+    const unsigned short* base = sb + (2 * rr) * PW3 + wo * 6;
+    uint32_t u[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t lo = off[2 * j] >= 0 ? base[off[2 * j]] : 0u;
+      const uint32_t hi = off[2 * j + 1] >= 0 ? base[off[2 * j + 1]] : 0u;
+      u[j] = lo | (hi << 16);
     }
-    *reinterpret_cast<uint4*>(out + (long long)wo * ldk + v8 * 8) = pack8(f);
+    *reinterpret_cast<uint4*>(cols + (((long long)n * Ho + ho) * Wo + wo) * ldk + v8 * 8) =
+        make_uint4(u[0], u[1], u[2], u[3]);
   }
 }
 
@@ -142,9 +161,9 @@ extern "C" int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int
 extern "C" int b200dt_stem_im2col(const float* x, void* cols, int NB, int H, int W, int ldk,
                                   void* stream) {
   if ((H | W) & 1 || ldk < 152 || (ldk % 8)) return -3;
-  const size_t smem = sizeof(float) * 7 * 3 * (W + 6);
-  if (smem > 48 * 1024) return -3;
-  stem_im2col_kernel<<<dim3(H / 2, NB), 256, smem, (cudaStream_t)stream>>>(
+  const size_t smem = sizeof(unsigned short) * (2 * kStemRows + 5) * 3 * (W + 6);
+  if (smem > 48 * 1024 || ldk / 8 > 256) return -3;
+  stem_im2col_kernel<<<dim3((H / 2 + kStemRows - 1) / kStemRows, NB), 256, smem, (cudaStream_t)stream>>>(
       x, reinterpret_cast<__nv_bfloat16*>(cols), H, W, ldk);
   return (int)cudaGetLastError();
 }

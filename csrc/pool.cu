@@ -46,42 +46,61 @@ maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, uint2* __
   }
 }
 
-// One thread per input pixel x 8 channels: gather from the (at most four) windows covering it.
+// One thread per 2x2 input patch x 8 channels.  The patch with origin (2k, 2l) is covered by the
+// windows (k, l), (k, l+1), (k+1, l), (k+1, l+1) only, so four (arg-max, dy) reads produce four
+// outputs (the per-pixel formulation needs nine); no atomics: every input pixel has one writer.
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const uint4* __restrict__ dy, const uint2* __restrict__ argmax,
                    uint4* __restrict__ dx, int NB, int H, int W, int C) {
   const int Ho = H / 2, Wo = W / 2, cv = C / 8;
-  const long long total = (long long)NB * H * W * cv;
+  const long long total = (long long)NB * Ho * Wo * cv;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % cv);
     long long pix = i / cv;
-    const int w = (int)(pix % W); pix /= W;
-    const int h = (int)(pix % H);
-    const int n = (int)(pix / H);
-    float g[8];
+    const int l = (int)(pix % Wo); pix /= Wo;
+    const int k = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float g[4][8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] = 0.f;
-    // windows ho with 2*ho - 1 <= h <= 2*ho + 1
-    for (int ho = (h) / 2; ho <= (h + 1) / 2; ++ho) {
-      if (ho < 0 || ho >= Ho) continue;
-      const int r = h - (ho * 2 - 1);
-      for (int wo = (w) / 2; wo <= (w + 1) / 2; ++wo) {
-        if (wo < 0 || wo >= Wo) continue;
-        const int s = w - (wo * 2 - 1);
-        const uint32_t code = r * 3 + s;
-        const long long o = (((long long)n * Ho + ho) * Wo + wo) * cv + c;
-        const uint2 a = argmax[o];
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[q][j] = 0.f;
+    // window (k + a, l + b) reaches patch pixel q = 2*py + px with arg-max code kCode[a][b][q]
+    // (code = r*3 + s of the window element; 255 = the window does not cover that pixel)
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      if (k + a >= Ho) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        if (l + b >= Wo) continue;
+        const long long o = (((long long)n * Ho + (k + a)) * Wo + (l + b)) * cv + c;
+        const uint2 am = argmax[o];
         float d[8];
         unpack8(ld_nc_v4(dy + o), d);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t aj = ((j < 4 ? a.x : a.y) >> ((j & 3) * 8)) & 0xff;
-          if (aj == code) g[j] += d[j];
+        for (int py = 0; py < 2; ++py) {
+          const int r = 2 * (0 - a) + py + 1;          // row of the pixel inside window k + a
+          if (r < 0 || r > 2 || (a == 1 && py == 0)) continue;
+#pragma unroll
+          for (int px = 0; px < 2; ++px) {
+            const int sidx = 2 * (0 - b) + px + 1;
+            if (sidx < 0 || sidx > 2 || (b == 1 && px == 0)) continue;
+            const uint32_t code = r * 3 + sidx;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t aj = ((j < 4 ? am.x : am.y) >> ((j & 3) * 8)) & 0xff;
+              if (aj == code) g[py * 2 + px][j] += d[j];
+            }
+          }
         }
       }
     }
-    dx[i] = pack8(g);
+#pragma unroll
+    for (int py = 0; py < 2; ++py)
+#pragma unroll
+      for (int px = 0; px < 2; ++px)
+        dx[(((long long)n * H + 2 * k + py) * W + 2 * l + px) * cv + c] = pack8(g[py * 2 + px]);
   }
 }
 
@@ -158,7 +177,7 @@ extern "C" int b200dt_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, 
 extern "C" int b200dt_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int NB,
                                        int H, int W, int C, void* stream) {
   if ((C % 8) || ((H | W) & 1)) return -3;
-  const long long total = (long long)NB * H * W * (C / 8);
+  const long long total = (long long)NB * (H / 2) * (W / 2) * (C / 8);   // one thread per 2x2 patch
   maxpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint2*>(argmax),
       reinterpret_cast<uint4*>(dx), NB, H, W, C);

@@ -84,6 +84,7 @@ class _Conv2d(torch.autograd.Function):
         ctx.save_for_backward(x, weight)
         ctx.stride = stride
         ctx.with_stats = with_stats
+        ctx.set_materialize_grads(False)      # no zero tensor for the statistics output in backward
         if with_stats:
             # per-channel sum / sum of squares of the output, accumulated in the conv epilogue
             sums = NV.bn_sums_buffer(weight.shape[0], x.device)
@@ -94,6 +95,8 @@ class _Conv2d(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy, *unused):
+        if dy is None:
+            return None, None, None, None
         x, weight = ctx.saved_tensors
         R = weight.shape[1]
         dy = dy.contiguous()
@@ -122,6 +125,7 @@ class _ConvSkip(torch.autograd.Function):
         wb = _shadow(weight)
         ctx.save_for_backward(x, weight)
         ctx.stride = stride
+        ctx.set_materialize_grads(False)
         if with_stats:
             sums = NV.bn_sums_buffer(weight.shape[0], x.device)
             y = NV.conv2d_fprop(x, wb, stride=stride, bn_sums=sums)
@@ -161,6 +165,7 @@ class _ConvDual(torch.autograd.Function):
     def forward(ctx, x, w1, w2, stride1, stride2):
         ctx.save_for_backward(x, w1, w2)
         ctx.strides = (stride1, stride2)
+        ctx.set_materialize_grads(False)
         s1 = NV.bn_sums_buffer(w1.shape[0], x.device)
         s2 = NV.bn_sums_buffer(w2.shape[0], x.device)
         y1 = NV.conv2d_fprop(x, _shadow(w1), stride=stride1, bn_sums=s1)
@@ -172,15 +177,17 @@ class _ConvDual(torch.autograd.Function):
     def backward(ctx, dy1, _d1, dy2, _d2):
         x, w1, w2 = ctx.saved_tensors
         st1, st2 = ctx.strides
-        dy1 = dy1.contiguous()
-        dy2 = dy2.contiguous()
+        dy1 = dy1.contiguous() if dy1 is not None else None
+        dy2 = dy2.contiguous() if dy2 is not None else None
         dx = dw1 = dw2 = None
         if ctx.needs_input_grad[0]:
-            dx = NV.conv2d_dgrad(dy1, _shadow(w1), x.shape, w1.shape[1], stride=st1)
-            dx = NV.conv2d_dgrad(dy2, _shadow(w2), x.shape, w2.shape[1], stride=st2, accumulate_into=dx)
-        if ctx.needs_input_grad[1]:
+            if dy1 is not None:
+                dx = NV.conv2d_dgrad(dy1, _shadow(w1), x.shape, w1.shape[1], stride=st1)
+            if dy2 is not None:
+                dx = NV.conv2d_dgrad(dy2, _shadow(w2), x.shape, w2.shape[1], stride=st2, accumulate_into=dx)
+        if ctx.needs_input_grad[1] and dy1 is not None:
             dw1 = NV.conv2d_wgrad(x, dy1, w1.shape[1], stride=st1)
-        if ctx.needs_input_grad[2]:
+        if ctx.needs_input_grad[2] and dy2 is not None:
             dw2 = NV.conv2d_wgrad(x, dy2, w2.shape[1], stride=st2)
         return dx, dw1, dw2, None, None
 
@@ -200,6 +207,7 @@ class _StemConv(torch.autograd.Function):
         wk = torch.zeros((weight.shape[0], NV.STEM_LDK), device=x.device, dtype=BF16)
         wk[:, :147] = weight.detach().reshape(weight.shape[0], 147)
         sums = NV.bn_sums_buffer(weight.shape[0], x.device) if with_stats else None
+        ctx.set_materialize_grads(False)
         y = NV.gemm_tn(cols, wk, bn_sums=sums)
         # the patch matrix is kept for the weight gradient (memory is cheap on a 180 GB part;
         # re-gathering it costs a full extra pass over the input)
@@ -214,7 +222,7 @@ class _StemConv(torch.autograd.Function):
     def backward(ctx, dy, *unused):
         cols, weight = ctx.saved_tensors
         dw = None
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and dy is not None:
             dy2 = dy.reshape(-1, weight.shape[0]).contiguous()
             dwk = NV.gemm_nt_reduce(dy2, cols)               # [64, 160]
             dw = dwk[:, :147].reshape(weight.shape).contiguous()

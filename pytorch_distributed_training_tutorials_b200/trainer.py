@@ -47,6 +47,12 @@ class Trainer:
             from .parallel.ddp import DistributedDataParallel
             ids = [gpu_id] if self.device.type == "cuda" else None
             self.model = DistributedDataParallel(self.model, device_ids=ids, **(ddp_kwargs or {}))
+        if self.cuda_graph and getattr(self.model, "world_size", 1) > 1 and not getattr(self.model, "_use_kernels", True):
+            # the NCCL / gloo fallback of the reducer is host-driven (async work handles, waits): it is
+            # not captured; only the peer-memory kernels replay from a graph
+            import warnings
+            warnings.warn("cuda_graph=True needs the fused peer-memory all-reduce; running eager steps instead")
+            self.cuda_graph = False
 
     def _run_batch(self, xs, ys):
         if self.cuda_graph:
