@@ -140,7 +140,8 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
                 const float* __restrict__ beta, float* running_mean, float* running_var,
                 float* save_mean, float* save_invstd, const float* __restrict__ in_mean,
                 const float* __restrict__ in_var, long long rows, int C, float eps, float momentum,
-                int relu, int cols, int rowlanes, long long* batches_tracked) {
+                int relu, int cols, int rowlanes, long long* batches_tracked,
+                unsigned char* __restrict__ relu_mask) {
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
@@ -200,6 +201,13 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
         for (int j = 0; j < 8; ++j) f[j] += g[j];
       }
       if (relu) {
+        if (relu_mask != nullptr) {
+          // one bit per element: backward masks the gradient from this byte instead of re-reading y
+          unsigned m = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+          relu_mask[rr * cv + col] = (unsigned char)m;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
       }
@@ -208,7 +216,8 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
   }
 }
 
-// kMask: 0 = no ReLU, 1 = mask from the saved output y, 2 = mask recomputed from x
+// kMask: 0 = no ReLU, 1 = mask from the saved output y, 2 = mask recomputed from x,
+// 3 = mask from the forward's bit mask (y points at one byte per 8 channels)
 template <int kMask>
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
@@ -246,6 +255,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
           vg[u] = ld_nc_v4(dy + rr * cv + col);
           vx[u] = ld_nc_v4(x + rr * cv + col);
           if (kMask == 1) vy[u] = ld_nc_v4(y + rr * cv + col);
+          if (kMask == 3) vy[u].x = reinterpret_cast<const unsigned char*>(y)[rr * cv + col];
         }
       }
 #pragma unroll
@@ -263,6 +273,9 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
           unpack8(vy[u], yv);
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        } else if (kMask == 3) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = ((vy[u].x >> j) & 1u) ? g[j] : 0.f;
         }
         if (dres != nullptr) dres[rr * cv + col] = pack8(g);
 #pragma unroll
@@ -366,14 +379,14 @@ extern "C" int b200dt_bn_apply(const void* x, const void* residual, void* y, con
                                const float* gamma, const float* beta, float* running_mean,
                                float* running_var, float* save_mean, float* save_invstd,
                                long long rows, int C, float eps, float momentum, int relu,
-                               long long* batches_tracked, void* stream) {
+                               long long* batches_tracked, unsigned char* relu_mask, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   Slab s = make_slab(rows, C, target_blocks());
   bn_apply_kernel<true><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), sums, gamma, beta, running_mean, running_var, save_mean,
       save_invstd, nullptr, nullptr, rows, C, eps, momentum, relu, s.cols_per_block,
-      s.rows_per_iter, batches_tracked);
+      s.rows_per_iter, batches_tracked, relu ? relu_mask : nullptr);
   return (int)cudaGetLastError();
 }
 
@@ -386,7 +399,7 @@ extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y
   bn_apply_kernel<false><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), nullptr, gamma, beta, nullptr, nullptr, nullptr, nullptr, mean,
-      var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter, nullptr);
+      var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter, nullptr, nullptr);
   return (int)cudaGetLastError();
 }
 
@@ -396,18 +409,20 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
                                     long long rows, int C, int relu, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   if (relu && y == nullptr && (gamma == nullptr || beta == nullptr)) return -3;
+  if (relu == 2 && (y == nullptr || dres == nullptr)) return -3;   // bit-mask mode materialises the masked gradient
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * (2 * C * kRep + 1), st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
-  const int mask = !relu ? 0 : (y != nullptr ? 1 : 2);
+  const int mask = !relu ? 0 : (relu == 2 ? 3 : (y != nullptr ? 1 : 2));
 #define B200_LAUNCH_REDUCE(M)                                                                      \
   bn_bwd_reduce_kernel<M><<<s.grid, kBnThreads, smem, st>>>(                                       \
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
       reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
       reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter)
-  if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1); else B200_LAUNCH_REDUCE(2);
+  if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1);
+  else if (mask == 2) B200_LAUNCH_REDUCE(2); else B200_LAUNCH_REDUCE(3);
 #undef B200_LAUNCH_REDUCE
   return (int)cudaGetLastError();
 }

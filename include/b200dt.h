@@ -70,18 +70,21 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
 /* y = act(gamma * (x - mean) * invstd + beta (+ residual)); writes mean/invstd (fp32 [C] each)
  * and updates running stats with `momentum` (unbiased variance), all from `sums`.
- * batches_tracked (optional, device int64): incremented by one, like nn.BatchNorm's counter. */
+ * batches_tracked (optional, device int64): incremented by one, like nn.BatchNorm's counter.
+ * relu_mask (optional, rows*C/8 bytes, relu only): bit j of byte [row][c/8] = output element > 0. */
 int b200dt_bn_apply(const void* x, const void* residual, void* y, const float* sums,
                     const float* gamma, const float* beta, float* running_mean, float* running_var,
                     float* save_mean, float* save_invstd, long long rows, int C, float eps,
-                    float momentum, int relu, long long* batches_tracked, void* stream);
+                    float momentum, int relu, long long* batches_tracked, unsigned char* relu_mask,
+                    void* stream);
 /* Inference-style apply with given statistics. */
 int b200dt_bn_apply_eval(const void* x, const void* residual, void* y, const float* gamma,
                          const float* beta, const float* mean, const float* var, long long rows,
                          int C, float eps, int relu, void* stream);
 /* Backward phase 1: g = dy * (y > 0 if relu); sums[0..C) = sum g, sums[C..2C) = sum g * xhat;
  * optionally writes g to dres (gradient of the residual branch). */
-/* With relu != 0 and y == NULL the mask is recomputed from x, gamma, beta (no residual case). */
+/* With relu != 0 and y == NULL the mask is recomputed from x, gamma, beta (no residual case).
+ * relu == 2: y points at the bit mask written by b200dt_bn_apply (dres is required). */
 int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x, const float* save_mean,
                          const float* save_invstd, const float* gamma, const float* beta, float* sums,
                          void* dres, long long rows, int C, int relu, void* stream);

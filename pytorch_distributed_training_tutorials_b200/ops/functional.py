@@ -242,18 +242,23 @@ class _BatchNorm(torch.autograd.Function):
         Cc = shp[-1]
         x2 = x.reshape(-1, Cc)
         r2 = residual.reshape(-1, Cc) if residual is not None else None
+        mask = None
         if training:
             if sums is None:
                 sums = NV.bn_stats(x2)
+            if relu and residual is not None and x2.numel() % 8 == 0:
+                # with a residual input the ReLU mask cannot be recomputed from x: keep one BIT per element
+                mask = torch.empty(x2.numel() // 8, device=x2.device, dtype=torch.uint8)
             y, mean, invstd = NV.bn_apply(x2, r2, sums, gamma.detach(), beta.detach(), running_mean,
-                                          running_var, eps, momentum, relu, tracked)
+                                          running_var, eps, momentum, relu, tracked, mask)
         else:
             y = NV.bn_apply_eval(x2, r2, gamma.detach(), beta.detach(), running_mean, running_var, eps, relu)
             mean = running_mean
             invstd = torch.rsqrt(running_var + eps)
-        # without a residual input the ReLU mask can be recomputed from x in backward: y is not kept
-        keep_y = relu and residual is not None
-        ctx.save_for_backward(x2, y if keep_y else None, gamma, beta, mean, invstd)
+        # without a residual input the ReLU mask is recomputed from x in backward, with one the bit
+        # mask is kept: the output y itself is never saved by this op
+        keep_y = relu and residual is not None and mask is None
+        ctx.save_for_backward(x2, y if keep_y else None, gamma, beta, mean, invstd, mask)
         ctx.relu = relu
         ctx.has_res = residual is not None
         ctx.shape = shp
@@ -262,14 +267,14 @@ class _BatchNorm(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y, gamma, beta, mean, invstd = ctx.saved_tensors
+        x2, y, gamma, beta, mean, invstd, mask = ctx.saved_tensors
         Cc = ctx.shape[-1]
         dy2 = dy.reshape(-1, Cc).contiguous()
         if not ctx.training:
             raise RuntimeError("backward through eval-mode BatchNorm is not supported")
         want_res = ctx.has_res and ctx.needs_input_grad[3]
         dx, dgamma, dbeta, dres = NV.bn_backward(dy2, y, x2, mean, invstd, gamma.detach(), ctx.relu, want_res,
-                                                 beta=beta.detach())
+                                                 beta=beta.detach(), relu_mask=mask)
         return (dx.view(ctx.shape), dgamma, dbeta, dres.view(ctx.shape) if dres is not None else None,
                 None, None, None, None, None, None, None, None)
 

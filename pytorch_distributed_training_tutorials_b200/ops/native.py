@@ -196,10 +196,17 @@ def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
 
 
 def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, momentum, relu,
-             batches_tracked: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """``batches_tracked``: optional int64 device scalar the kernel increments (no launch of its own)."""
+             batches_tracked: Optional[torch.Tensor] = None, relu_mask: Optional[torch.Tensor] = None
+             ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """``batches_tracked``: optional int64 device scalar the kernel increments (no launch of its own).
+    ``relu_mask``: optional uint8 ``[rows * C / 8]`` that receives one bit per output element (> 0);
+    ``bn_backward(..., relu_mask=)`` then masks the gradient without re-reading the output."""
     if batches_tracked is not None:
         _need(batches_tracked, torch.int64, "batches_tracked")
+    if relu_mask is not None:
+        _need(relu_mask, torch.uint8, "relu_mask")
+        if relu_mask.numel() != x2d.numel() // 8:
+            raise ValueError("relu_mask needs rows * C / 8 bytes")
     rows, Cc = x2d.shape
     y = torch.empty_like(x2d)
     save_mean = torch.empty(Cc, device=x2d.device, dtype=F32)
@@ -208,7 +215,7 @@ def bn_apply(x2d, residual, sums, gamma, beta, running_mean, running_var, eps, m
         check(lib().b200dt_bn_apply(ptr(x2d), ptr(residual), ptr(y), ptr(sums), ptr(gamma), ptr(beta),
                                     ptr(running_mean), ptr(running_var), ptr(save_mean), ptr(save_invstd),
                                     rows, Cc, eps, momentum, int(relu), ptr(batches_tracked),
-                                    stream_ptr(x2d.device)), "bn_apply")
+                                    ptr(relu_mask), stream_ptr(x2d.device)), "bn_apply")
     return y, save_mean, save_invstd
 
 
@@ -221,11 +228,28 @@ def bn_apply_eval(x2d, residual, gamma, beta, mean, var, eps, relu) -> torch.Ten
     return y
 
 
-def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_dres: bool, beta=None):
+def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_dres: bool, beta=None,
+                relu_mask: Optional[torch.Tensor] = None):
     """Returns (dx, dgamma, dbeta, dres or None). With ``relu`` and ``y2d is None`` the ReLU mask is
-    recomputed from ``x2d`` (needs ``beta``; only valid when the forward had no residual input)."""
+    recomputed from ``x2d`` (needs ``beta``; only valid when the forward had no residual input);
+    with ``relu_mask`` (from ``bn_apply``) it is read from one byte per eight channels."""
     rows, Cc = x2d.shape
     dev = x2d.device
+    if relu and relu_mask is not None:
+        dres = torch.empty_like(dy2d)
+        dx = torch.empty_like(x2d)
+        sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=dev, dtype=F32)
+        dgamma = torch.empty(Cc, device=dev, dtype=F32)
+        dbeta = torch.empty(Cc, device=dev, dtype=F32)
+        with on_device(dev):
+            st = stream_ptr(dev)
+            check(lib().b200dt_bn_bwd_reduce(ptr(dy2d), ptr(relu_mask), ptr(x2d), ptr(save_mean), ptr(save_invstd),
+                                             ptr(gamma), ptr(beta), ptr(sums), ptr(dres), rows, Cc, 2, st),
+                  "bn_bwd_reduce")
+            check(lib().b200dt_bn_bwd_apply(ptr(dres), None, ptr(x2d), ptr(save_mean), ptr(save_invstd),
+                                            ptr(gamma), ptr(beta), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta),
+                                            rows, Cc, 0, st), "bn_bwd_apply")
+        return dx, dgamma, dbeta, (dres if want_dres else None)
     sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=dev, dtype=F32)
     dres = torch.empty_like(dy2d) if want_dres else None
     dx = torch.empty_like(x2d)

@@ -207,6 +207,17 @@ def test_batchnorm(rows, C, relu, res):
     assert rel_err(dbeta, bref.grad) < 2e-2
     if res:
         assert rel_err(dres, rr.grad) < 2e-2
+    if relu and res and (rows * C) % 8 == 0:
+        # bit-mask variant: the forward writes one bit per element, backward never reads y;
+        # the step counter is bumped by the same kernel
+        mask = torch.empty(rows * C // 8, device=dev(), dtype=torch.uint8)
+        tracked = torch.tensor(41, device=dev(), dtype=torch.int64)
+        y3, _, _ = NV.bn_apply(x, r, sums, g, b, rm.clone(), rv.clone(), 1e-5, 0.1, relu, tracked, mask)
+        assert torch.equal(y3, y) and int(tracked) == 42
+        dx3, dg3, db3, dres3 = NV.bn_backward(dy, None, x, mean, invstd, g, relu, True, beta=b, relu_mask=mask)
+        # the mask is taken before the bf16 rounding of y: elements that round to +0 differ, nothing else
+        assert rel_err(dx3, dx) < 2e-3 and rel_err(dres3, dres) < 2e-3
+        assert rel_err(dg3, dgamma) < 2e-3 and rel_err(db3, dbeta) < 2e-3
 
 
 def test_pools():
