@@ -68,6 +68,10 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
  * apply kernels read) followed by one ticket word: 2*C*B200DT_BN_REPLICAS + 1 floats. */
 #define B200DT_BN_REPLICAS 16
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
+/* Backward of y = relu(linear): g = dy * (y > 0) (bf16, y == g == NULL skips the mask) and
+ * db[C] = column sums of g in fp32 (db == NULL skips them); one pass over [rows, C], C % 8 == 0. */
+int b200dt_relu_bwd_bias(const void* dy, const void* y, void* g, float* db, long long rows, int C,
+                         void* stream);
 /* y = act(gamma * (x - mean) * invstd + beta (+ residual)); writes mean/invstd (fp32 [C] each)
  * and updates running stats with `momentum` (unbiased variance), all from `sums`.
  * batches_tracked (optional, device int64): incremented by one, like nn.BatchNorm's counter.

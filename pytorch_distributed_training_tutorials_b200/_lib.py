@@ -55,6 +55,7 @@ _SIGS = {
     "b200dt_nchw_f32_to_nhwc_bf16": [vp, vp, i32, i32, i32, i32, vp],
     "b200dt_bn_stats": [vp, vp, i64, i32, vp],
     "b200dt_bn_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp, vp, vp],
+    "b200dt_relu_bwd_bias": [vp, vp, vp, vp, i64, i32, vp],
     "b200dt_bn_apply_eval": [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp],
     "b200dt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
     "b200dt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],

@@ -52,10 +52,17 @@ class _Linear(torch.autograd.Function):
         x2, weight, y = ctx.saved_tensors
         N, Kf = weight.shape
         dy2 = dy.reshape(-1, N)
-        if ctx.relu:
-            dy2 = dy2 * (y > 0)
-        dyb = dy2.to(BF16).contiguous()
         dx = dw = db = None
+        want_db = ctx.has_bias and ctx.needs_input_grad[2]
+        if N % 8 == 0 and (ctx.relu or want_db) and (not ctx.relu or y.dtype == BF16):
+            # ReLU mask and bias gradient in one pass (bf16 in, bf16 out, fp32 column sums)
+            dyb, db = NV.relu_bwd_bias(dy2.to(BF16).contiguous(), y.reshape(-1, N) if ctx.relu else None, want_db)
+            dy2 = dyb
+            want_db = False
+        else:
+            if ctx.relu:
+                dy2 = dy2 * (y > 0)
+            dyb = dy2.to(BF16).contiguous()
         if ctx.needs_input_grad[0]:
             if N % 8 == 0:
                 # W [out, in] is consumed in place as the MN-major B operand: no transposed copy
@@ -67,7 +74,7 @@ class _Linear(torch.autograd.Function):
                 dw = NV.gemm_nt_reduce(dyb, x2)
             else:
                 dw = dy2.float().t() @ x2.float()
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+        if want_db:
             db = dy2.float().sum(0)
         return dx, dw, db, None, None
 

@@ -79,6 +79,24 @@ def gemm_nt_reduce(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor]
     return out
 
 
+def relu_bwd_bias(dy: torch.Tensor, y: Optional[torch.Tensor], want_bias_grad: bool):
+    """Backward glue of ``relu(linear)`` in one pass over ``[rows, C]`` bf16: returns
+    ``(g, db)`` with ``g = dy * (y > 0)`` (``dy`` itself when ``y`` is None) and ``db`` the fp32 column sums."""
+    _need(dy, BF16, "dy")
+    rows, Cc = dy.shape
+    g = dy
+    if y is not None:
+        _need(y, BF16, "y")
+        g = torch.empty_like(dy)
+    db = torch.empty(Cc, device=dy.device, dtype=F32) if want_bias_grad else None
+    if y is None and db is None:
+        return g, None
+    with on_device(dy.device):
+        check(lib().b200dt_relu_bwd_bias(ptr(dy), ptr(y), ptr(g) if y is not None else None, ptr(db), rows, Cc,
+                                         stream_ptr(dy.device)), "relu_bwd_bias")
+    return g, db
+
+
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool = False,
                  bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
     _need(x, BF16, "x"); _need(w, BF16, "w")

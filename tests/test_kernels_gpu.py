@@ -220,6 +220,47 @@ def test_batchnorm(rows, C, relu, res):
         assert rel_err(dg3, dgamma) < 2e-3 and rel_err(db3, dbeta) < 2e-3
 
 
+@pytest.mark.parametrize("rows,C", [(2048, 4096), (1000, 24), (37, 8), (513, 1000)])
+def test_relu_bwd_bias(rows, C):
+    torch.manual_seed(21)
+    dy = torch.randn(rows, C, device=dev()).bfloat16()
+    y = torch.relu(torch.randn(rows, C, device=dev())).bfloat16()
+    g, db = NV.relu_bwd_bias(dy, y, True)
+    want = dy.float() * (y > 0)
+    assert torch.equal(g.float(), want)
+    assert torch.allclose(db, want.sum(0), rtol=1e-4, atol=1e-3 * rows ** 0.5)
+    g2, db2 = NV.relu_bwd_bias(dy, None, True)
+    assert g2 is dy and torch.allclose(db2, dy.float().sum(0), rtol=1e-4, atol=1e-3 * rows ** 0.5)
+    g3, db3 = NV.relu_bwd_bias(dy, y, False)
+    assert db3 is None and torch.equal(g3, g)
+
+
+@pytest.mark.parametrize("relu,out_fp32,bias", [(True, False, True), (False, True, True), (True, True, True), (False, False, False)])
+def test_linear_autograd_matches_torch(relu, out_fp32, bias):
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    torch.manual_seed(22)
+    x = torch.randn(300, 256, device=dev()).bfloat16().float().requires_grad_(True)
+    w = (torch.randn(136, 256, device=dev()) / 16).bfloat16().float().requires_grad_(True)
+    b = torch.randn(136, device=dev()).requires_grad_(True) if bias else None
+    y = Fn.linear(x, w, b, relu, out_fp32)
+    assert y.dtype == (torch.float32 if out_fp32 else torch.bfloat16)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    got = (x.grad.clone(), w.grad.clone(), b.grad.clone() if bias else None)
+    x.grad = None; w.grad = None
+    if bias:
+        b.grad = None
+    ref = F.linear(x, w, b)
+    if relu:
+        ref = torch.relu(ref)
+    assert rel_err(y, ref) < 1e-2
+    ref.backward(dy.float() * (y.float() > 0) if relu else dy.float())   # same mask as the bf16 output
+    assert rel_err(got[0], x.grad) < 1.5e-2
+    assert rel_err(got[1], w.grad) < 1.5e-2
+    if bias:
+        assert rel_err(got[2], b.grad) < 1e-2
+
+
 def test_pools():
     torch.manual_seed(5)
     x = torch.randn(4, 32, 32, 64, device=dev()).bfloat16()
