@@ -175,6 +175,7 @@ def run_ours(args, rank, world, local):
     trainer = Trainer(model, train_dataloader=None, optimizer=optimizer, gpu_id=local, wrap_ddp=True,
                       ddp_kwargs=dict(allreduce=args.allreduce, comm_dtype=args.comm_dtype,
                                       max_comm_blocks=args.comm_blocks,
+                                      gradient_as_bucket_view=not args.no_grad_views,
                                       broadcast_buffers=not args.no_broadcast_buffers),
                       cuda_graph=not args.no_graph)
     host_x, host_y = make_host_batches(2, args.batch_size, args.image, args.classes, seed=rank)
@@ -283,6 +284,8 @@ def main() -> None:
     ap.add_argument("--comm-dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--comm-blocks", type=int, default=32, help="CTAs of the fused all-reduce kernel (diagnostics)")
+    ap.add_argument("--no-grad-views", action="store_true",
+                    help="keep gradients outside the symmetric arena (copy-in / copy-out around the all-reduce)")
     ap.add_argument("--no-broadcast-buffers", action="store_true", help="skip the per-forward buffer broadcast (diagnostics)")
     ap.add_argument("--e2e-sync", action="store_true",
                     help="end-to-end number through the synchronous Trainer.step instead of the prefetching run_batches")

@@ -52,6 +52,14 @@ def main():
             table = coll.TensorTable([n], dev, False, False, target_blocks=args.blocks)
             table.bind([x], stream)
             row[m + "_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks), iters, dev)
+        # tensors that live in the symmetric arena (the DDP gradient-view mode): no copy-in / copy-out
+        table = coll.TensorTable([n], dev, False, False, target_blocks=args.blocks)
+        (xv,) = coll.stage_views(arena, table, [(n,)])
+        xv.copy_(x)
+        table.bind([xv], stream)
+        m = "nvls" if arena.has_multicast else "twoshot"
+        row[m + "_inplace_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks,
+                                                           in_place=True), iters, dev)
         if size >= (1 << 20):
             table = coll.TensorTable([n], dev, True, False, target_blocks=args.blocks)
             table.bind([x], stream)
@@ -62,7 +70,8 @@ def main():
         size *= 4
     if rank == 0:
         f = 2 * (world - 1) / world
-        keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_bf16wire_ms", "nvls_bf16wire_ms") if any(k in r for r in rows)]
+        keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_inplace_ms", "nvls_inplace_ms",
+                            "twoshot_bf16wire_ms", "nvls_bf16wire_ms") if any(k in r for r in rows)]
         print("| bytes | " + " | ".join(k[:-3] + " us / busbw GB/s" for k in keys) + " |")
         print("|---|" + "---|" * len(keys))
         for r in rows:

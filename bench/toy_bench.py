@@ -91,7 +91,8 @@ def main():
         dev, n, rank = st.device, st.world_size, st.rank
         B = args.per_gpu_batch
         x = torch.randn(B, IN, device=dev); y = torch.randn(B, OUT, device=dev)
-        mine = b2.DistributedDataParallel(MLP(IN, HID, DEPTH, OUT).to(dev), device_ids=[dev.index])
+        mine = b2.DistributedDataParallel(MLP(IN, HID, DEPTH, OUT).to(dev), device_ids=[dev.index],
+                                          gradient_as_bucket_view=True)
         opt = b2.FusedSGD(mine.parameters(), lr=1e-4)
         from pytorch_distributed_training_tutorials_b200.utils.graph import GraphedTrainStep
         g = GraphedTrainStep(mine, Fn.mse_loss, opt, x, y)

@@ -54,6 +54,7 @@ struct CollArgs {
   int sig_base;             // first signal word this launch may use
   int* status;
   unsigned long long spin_limit;
+  int in_place;             // tensors live (or are copied unscaled) in the staging region; the result stays there
 };
 
 constexpr int kCollThreads = 512;
@@ -207,6 +208,7 @@ __device__ __forceinline__ void twoshot_chunk(const CollArgs& a, const CollChunk
   const long long v_beg = a.rank * per;
   const long long v_end = min(nvec, v_beg + per);
   const long long byte0 = a.stage_base + ch.stage_off * esz;
+  const float post = a.in_place ? a.scale : 1.f;      // in-place mode scales the SUM (inputs are raw)
   for (long long v0 = v_beg + threadIdx.x; v0 < v_end; v0 += (long long)VU * blockDim.x) {
     uint4 in[VU][W];
 #pragma unroll
@@ -234,6 +236,8 @@ __device__ __forceinline__ void twoshot_chunk(const CollArgs& a, const CollChunk
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[j] += f[j];
         }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] *= post;
         out = pack8(acc);
       } else {
         float x = 0.f, y = 0.f, z = 0.f, w = 0.f;
@@ -242,6 +246,7 @@ __device__ __forceinline__ void twoshot_chunk(const CollArgs& a, const CollChunk
           x += __uint_as_float(in[u][r].x); y += __uint_as_float(in[u][r].y);
           z += __uint_as_float(in[u][r].z); w += __uint_as_float(in[u][r].w);
         }
+        x *= post; y *= post; z *= post; w *= post;
         out = make_uint4(__float_as_uint(x), __float_as_uint(y), __float_as_uint(z), __float_as_uint(w));
       }
 #pragma unroll
@@ -264,6 +269,12 @@ coll_kernel(const __grid_constant__ CollArgs a) {
       const CollTensor tt = a.tensors[ch.tensor];
       const bool aligned = ((reinterpret_cast<uintptr_t>(tt.ptr) + (size_t)ch.start * esz_t) & 15) == 0;
       const int groups = (ch.len + 7) / 8;
+      // in-place mode: a tensor that already lives at its slot of the staging region is not
+      // touched at all; a stray one (small parameters) is copied unscaled, the sum is scaled in P1
+      if (a.in_place && reinterpret_cast<const char*>(tt.ptr) + (size_t)ch.start * esz_t ==
+                            my_stage + (size_t)ch.stage_off * esz_t)
+        continue;
+      const float pre = a.in_place ? 1.f : a.scale;
       if (kMode != kBcast) {
         // four groups per thread: all loads are issued before the first dependent store
         for (int g0 = threadIdx.x; g0 < groups; g0 += 4 * blockDim.x) {
@@ -279,9 +290,9 @@ coll_kernel(const __grid_constant__ CollArgs a) {
           for (int u = 0; u < 4; ++u) {
             const int g = g0 + u * blockDim.x;
             if (g < groups) {
-              if (a.scale != 1.f) {
+              if (pre != 1.f) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[u][j] *= a.scale;
+                for (int j = 0; j < 8; ++j) f[u][j] *= pre;
               }
               store8_stage(my_stage, ch.stage_off + g * 8, a.wire_bf16, f[u]);
             }
@@ -359,20 +370,38 @@ coll_kernel(const __grid_constant__ CollArgs a) {
         const long long e = ch.stage_off + (long long)g * 8;
         if (kMode == kNvls) {
           char* mcs = reinterpret_cast<char*>(a.mc) + a.stage_base;
+          const float post = a.in_place ? a.scale : 1.f;
           if (a.wire_bf16) {
             __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(mcs) + e;
-            const uint4 v = multimem_ld_reduce_bf16x8(p);
+            uint4 v = multimem_ld_reduce_bf16x8(p);
+            if (post != 1.f) {
+              float f[8];
+              unpack8(v, f);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[j] *= post;
+              v = pack8(f);
+            }
             multimem_st_v4(p, v);
           } else {
             float* p = reinterpret_cast<float*>(mcs) + e;
-            const uint4 v0 = multimem_ld_reduce_f32x4(p);
-            const uint4 v1 = multimem_ld_reduce_f32x4(p + 4);
+            uint4 v0 = multimem_ld_reduce_f32x4(p);
+            uint4 v1 = multimem_ld_reduce_f32x4(p + 4);
+            if (post != 1.f) {
+              v0 = make_uint4(__float_as_uint(__uint_as_float(v0.x) * post), __float_as_uint(__uint_as_float(v0.y) * post),
+                              __float_as_uint(__uint_as_float(v0.z) * post), __float_as_uint(__uint_as_float(v0.w) * post));
+              v1 = make_uint4(__float_as_uint(__uint_as_float(v1.x) * post), __float_as_uint(__uint_as_float(v1.y) * post),
+                              __float_as_uint(__uint_as_float(v1.z) * post), __float_as_uint(__uint_as_float(v1.w) * post));
+            }
             multimem_st_v4(p, v0);
             multimem_st_v4(p + 4, v1);
           }
         } else {
           float acc[8];
           reduce_group(a, e, acc);
+          if (a.in_place) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] *= a.scale;
+          }
 #pragma unroll
           for (int r = 0; r < B200DT_MAX_WORLD; ++r)
             if (r < a.world)
@@ -382,6 +411,7 @@ coll_kernel(const __grid_constant__ CollArgs a) {
     }
     if (a.world > 1) block_barrier(a);
   }
+  if (a.in_place && kMode != kBcast) return;     // the staging region IS the result (gradient views)
 
   // ---------------------------------------------------------------- P2: staging -> tensors
   for (int c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
@@ -459,9 +489,12 @@ extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t
                                   int rank, int world, int root, const void* tensors,
                                   const void* chunks, int n_chunks, long long stage_base_bytes,
                                   int tensor_bf16, int wire_bf16, float scale, int sig_base,
-                                  int grid, int* status, void* stream) {
+                                  int grid, int* status, int in_place, void* stream) {
   if (world < 1 || world > B200DT_MAX_WORLD || n_chunks <= 0) return world < 1 ? -3 : 0;
   if (mode == kNvls && mc == 0) return -4;
+  // in place: every rank overwrites the slice it owns, which only two-shot / NVLS make race-free,
+  // and the tensors must already have the wire dtype
+  if (in_place && (mode == kOneShot || mode == kBcast || (wire_bf16 != 0) != (tensor_bf16 != 0))) return -3;
   if (grid < 1) grid = 1;
   if (sig_base + grid * world > B200DT_SIGNAL_WORDS) return -5;
   CollArgs a{};
@@ -478,6 +511,7 @@ extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t
   a.tensor_bf16 = tensor_bf16; a.wire_bf16 = wire_bf16 || tensor_bf16;
   a.scale = scale; a.sig_base = sig_base; a.status = status;
   a.spin_limit = 1ull << 26;     // ~ tens of seconds of polling before giving up
+  a.in_place = in_place;
   cudaStream_t st = (cudaStream_t)stream;
   switch (mode) {
     case kOneShot: coll_kernel<kOneShot, 0><<<grid, kCollThreads, 0, st>>>(a); break;

@@ -171,14 +171,18 @@ int b200dt_multi_adam(const long long* meta, const int* chunks, int n_chunks, fl
  * required for mode 2). `tensors`: device array of {void* ptr; int64 numel}. `chunks`: device array
  * of {int32 tensor, int32 start, int32 len, int32 pad, int64 stage_off}; stage_off is in elements,
  * a multiple of 8. All ranks must pass identical chunk tables, `grid` and `sig_base`. `status`
- * (device int32) becomes non-zero if a peer did not arrive within the spin bound. */
+ * (device int32) becomes non-zero if a peer did not arrive within the spin bound.
+ * in_place != 0 (modes 1 and 2, wire dtype == tensor dtype): the staging region is the home of the
+ * tensors ("gradients as bucket views"): a tensor whose address already is its staging slot is not
+ * copied, others are copied in unscaled, `scale` is applied to the SUM, and nothing is copied back
+ * (the result is read from the staging region). */
 #define B200DT_SIGNAL_WORDS 8192
 #define B200DT_MAX_WORLD 8
 int b200dt_coll_chunk_bytes(void);
 int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t* sigs, uint64_t mc, int rank,
                        int world, int root, const void* tensors, const void* chunks, int n_chunks,
                        long long stage_base_bytes, int tensor_bf16, int wire_bf16, float scale,
-                       int sig_base, int grid, int* status, void* stream);
+                       int sig_base, int grid, int* status, int in_place, void* stream);
 /* fp32 gradient -> (scaled) bucket slot, optionally as bf16 (NCCL / gloo fallback copy-in). */
 int b200dt_scale_cast(const float* src, void* dst, long long n, float scale, int dst_bf16,
                       void* stream);

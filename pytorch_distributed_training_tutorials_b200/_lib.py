@@ -70,7 +70,7 @@ _SIGS = {
     "b200dt_multi_sgd": [vp, vp, i32, f32, f32, f32, i32, vp],
     "b200dt_multi_adam": [vp, vp, i32, f32, f32, f32, f32, f32, i32, f32, i32, vp],
     "b200dt_coll_launch": [i32, vp, vp, u64, i32, i32, i32, vp, vp, i32, i64, i32, i32, f32, i32,
-                           i32, vp, vp],
+                           i32, vp, i32, vp],
     "b200dt_scale_cast": [vp, vp, i64, f32, i32, vp],
     "b200dt_cast_to_f32": [vp, vp, i64, i32, vp],
     "b200dt_allreduce_local_emulate": [vp, i32, vp, i64, i32, f32, vp],

@@ -116,6 +116,13 @@ class TensorTable:
                 s += ln
         self.stage_elems = off
         self.stage_bytes = off * (2 if self.wire_bf16 else 4)
+        # element offset of every tensor inside the staging region (its chunks are contiguous)
+        self.tensor_offsets = []
+        seen = set()
+        for ti, s0, ln, o in rows:
+            if ti not in seen:
+                seen.add(ti)
+                self.tensor_offsets.append(o)
         self.n_chunks = len(rows)
         assert lib().b200dt_coll_chunk_bytes() == 24
         raw = torch.empty(max(len(rows), 1) * 3, dtype=torch.int64)
@@ -146,15 +153,37 @@ class TensorTable:
 
 
 def launch(mode: str, arena: SymmetricArena, table: TensorTable, scale: float, stream: torch.cuda.Stream,
-           root: int = 0, sig_base: int = 0, max_blocks: int = 32) -> None:
+           root: int = 0, sig_base: int = 0, max_blocks: int = 32, stage_base: int = 0,
+           in_place: bool = False) -> None:
+    """``stage_base``: byte offset of this table's staging region inside the arena.  ``in_place``: the
+    tensors' home IS that region (see ``stage_views``): no copy-in for resident tensors, no copy-out."""
     grid = table.grid(max_blocks)
-    if table.stage_bytes > arena.nbytes:
-        raise RuntimeError(f"bucket of {table.stage_bytes} bytes does not fit the {arena.nbytes}-byte arena")
+    if stage_base + table.stage_bytes > arena.nbytes:
+        raise RuntimeError(f"bucket of {table.stage_bytes} bytes at offset {stage_base} does not fit the "
+                           f"{arena.nbytes}-byte arena")
+    if in_place and mode not in ("twoshot", "nvls"):
+        raise ValueError("in-place all-reduce needs the two-shot or NVLS kernel")
     with torch.cuda.device(arena.device):
         check(lib().b200dt_coll_launch(MODE[mode], arena._bufs_c, arena._sigs_c, arena.multicast_ptr if mode in ("nvls", "bcast") else 0,
                                        arena.rank, arena.world, root, ptr(table.tensors), ptr(table.chunks),
-                                       table.n_chunks, 0, int(table.tensor_bf16), int(table.wire_bf16), scale,
-                                       sig_base, grid, ptr(arena.status), stream.cuda_stream), f"coll_launch[{mode}]")
+                                       table.n_chunks, int(stage_base), int(table.tensor_bf16), int(table.wire_bf16),
+                                       scale, sig_base, grid, ptr(arena.status), int(in_place),
+                                       stream.cuda_stream), f"coll_launch[{mode}]")
+
+
+def stage_views(arena: SymmetricArena, table: TensorTable, shapes: Sequence, stage_base: int = 0) -> List[torch.Tensor]:
+    """Tensors that LIVE in this rank's staging region at the slots ``table`` assigns to them: write the
+    data there (or let a kernel produce it there) and ``launch(..., in_place=True)`` reduces it without
+    the copy-in / copy-out passes -- the peer-memory analogue of NCCL user-buffer registration."""
+    dt = torch.bfloat16 if table.wire_bf16 else torch.float32
+    esz = 2 if table.wire_bf16 else 4
+    if stage_base % 16:
+        raise ValueError("stage_base must be a multiple of 16 bytes")
+    region = arena.buf[stage_base:stage_base + table.stage_bytes].view(dt)
+    out = []
+    for off, n, shp in zip(table.tensor_offsets, table.numels, shapes):
+        out.append(region[off:off + n].view(shp))
+    return out
 
 
 def all_reduce_(tensors: List[torch.Tensor], arena: SymmetricArena, mode: str = "auto", scale: float = 1.0,

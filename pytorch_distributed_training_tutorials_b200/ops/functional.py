@@ -30,6 +30,20 @@ def _shadow(w: torch.Tensor) -> torch.Tensor:
     return s
 
 
+def _grad_out(p: torch.Tensor) -> Optional[torch.Tensor]:
+    """Destination for a freshly computed weight gradient when DDP keeps gradients as views of its
+    symmetric arena (``gradient_as_bucket_view``): the kernel writes straight into the bucket slot and
+    autograd adopts that tensor as ``.grad``, so the all-reduce needs no copy-in.  None otherwise, and
+    while a gradient is being accumulated (then autograd must add, not overwrite)."""
+    slot = getattr(p, "_b200_grad_slot", None)
+    if slot is None or p.grad is not None:
+        return None
+    region, off = slot
+    if region.dtype != F32 or region.device != p.device:
+        return None
+    return region[off:off + p.numel()].view(p.shape)
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, relu, out_fp32):
@@ -71,7 +85,7 @@ class _Linear(torch.autograd.Function):
                 dx = (dy2.float() @ weight.detach()).view(ctx.x_shape).to(ctx.x_dtype)
         if ctx.needs_input_grad[1]:
             if N % 8 == 0 and Kf % 8 == 0:
-                dw = NV.gemm_nt_reduce(dyb, x2)
+                dw = NV.gemm_nt_reduce(dyb, x2, out=_grad_out(weight))
             else:
                 dw = dy2.float().t() @ x2.float()
         if want_db:
@@ -111,7 +125,7 @@ class _Conv2d(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = NV.conv2d_dgrad(dy, _shadow(weight), x.shape, R, stride=ctx.stride)
         if ctx.needs_input_grad[1]:
-            dw = NV.conv2d_wgrad(x, dy, R, stride=ctx.stride)
+            dw = NV.conv2d_wgrad(x, dy, R, stride=ctx.stride, out=_grad_out(weight))
         return dx, dw, None, None
 
 
@@ -153,7 +167,7 @@ class _ConvSkip(torch.autograd.Function):
                 dx = NV.conv2d_dgrad(dy.contiguous(), _shadow(weight), x.shape, R, stride=ctx.stride,
                                      accumulate_into=acc)
         if ctx.needs_input_grad[1] and dy is not None:
-            dw = NV.conv2d_wgrad(x, dy.contiguous(), R, stride=ctx.stride)
+            dw = NV.conv2d_wgrad(x, dy.contiguous(), R, stride=ctx.stride, out=_grad_out(weight))
         return dx, dw, None, None
 
 
@@ -193,9 +207,9 @@ class _ConvDual(torch.autograd.Function):
             if dy2 is not None:
                 dx = NV.conv2d_dgrad(dy2, _shadow(w2), x.shape, w2.shape[1], stride=st2, accumulate_into=dx)
         if ctx.needs_input_grad[1] and dy1 is not None:
-            dw1 = NV.conv2d_wgrad(x, dy1, w1.shape[1], stride=st1)
+            dw1 = NV.conv2d_wgrad(x, dy1, w1.shape[1], stride=st1, out=_grad_out(w1))
         if ctx.needs_input_grad[2] and dy2 is not None:
-            dw2 = NV.conv2d_wgrad(x, dy2, w2.shape[1], stride=st2)
+            dw2 = NV.conv2d_wgrad(x, dy2, w2.shape[1], stride=st2, out=_grad_out(w2))
         return dx, dw1, dw2, None, None
 
 

@@ -43,6 +43,8 @@ class _Bucket:
         self.work = None
         self.nbytes = 0
         self.mode = None
+        self.stage_base = 0          # byte offset of this bucket's region inside the arena
+        self.views = None            # gradient views living in that region (gradient_as_bucket_view)
 
 
 class DistributedDataParallel(nn.Module):
@@ -134,13 +136,17 @@ class DistributedDataParallel(nn.Module):
         # the construction-time broadcast stages parameters AND buffers (as 32-bit words) at once
         bufs = sum((b.numel() * b.element_size() // 4 + 8) // 8 * 8 * 4 for b in self.module.buffers())
         need = total + bufs + (1 << 20)
+        # gradients that LIVE in the arena get a region of their own behind the broadcast staging
+        self._grad_region = (need + 4095) // 4096 * 4096
+        if self.gradient_as_bucket_view:
+            need = self._grad_region + total + 256 * (len(self._params) + 64)
         try:
-            if st is not None and st.arena is not None and st.arena.nbytes >= need \
-                    and st.arena.group is self.process_group:
+            if not self.gradient_as_bucket_view and st is not None and st.arena is not None \
+                    and st.arena.nbytes >= need and st.arena.group is self.process_group:
                 self._arena = st.arena
             else:
                 self._arena = SymmetricArena(need, self.device, self.process_group)
-                if st is not None and st.arena is None:
+                if st is not None and st.arena is None and not self.gradient_as_bucket_view:
                     st.arena = self._arena
         except Exception as e:  # symmetric memory unavailable: say so loudly, fall back to NCCL
             self._use_kernels = False
@@ -214,7 +220,38 @@ class DistributedDataParallel(nn.Module):
                                            self.comm_dtype == "bf16", tb16, target_blocks=self.max_comm_blocks)
                 b.mode = coll.pick_mode(b.table.stage_bytes, self._arena, self.allreduce)
             out.append(b)
+        self._assign_grad_views(out)
         return out
+
+    def _views_possible(self) -> bool:
+        wire16 = self.comm_dtype == "bf16"
+        return (self.gradient_as_bucket_view and self._use_kernels and self._arena is not None
+                and all((p.dtype == torch.bfloat16) == wire16 for p in self._params))
+
+    def _assign_grad_views(self, buckets) -> None:
+        """gradient_as_bucket_view: every bucket owns a region of the symmetric arena and the
+        parameters' ``.grad`` become views of it.  Weight-gradient kernels write there directly
+        (``p._b200_grad_slot``), the all-reduce runs in place and nothing is copied back."""
+        for p in self._params:
+            if hasattr(p, "_b200_grad_slot"):
+                p._b200_grad_slot = None
+        if not self._views_possible():
+            return
+        from ..ops import collectives as coll
+        base = self._grad_region
+        for b in buckets:
+            b.stage_base = base
+            shapes = [self._params[j].shape for j in b.param_ids]
+            b.views = coll.stage_views(self._arena, b.table, shapes, base)
+            if b.mode == "oneshot":
+                b.mode = "twoshot"            # in place, every rank may only overwrite the slice it owns
+            region = self._arena.buf[base:base + b.table.stage_bytes].view(b.views[0].dtype)
+            for k, j in enumerate(b.param_ids):
+                p = self._params[j]
+                p._b200_grad_slot = (region, b.table.tensor_offsets[k])
+                if p.grad is not None:        # a stale view of the previous layout must not survive
+                    p.grad = p.grad.detach().clone()
+            base += (b.table.stage_bytes + 255) // 256 * 256
 
     def _rebuild_buckets(self) -> None:
         """Re-bucket in gradient-ready order with caps [1 MiB, bucket_cap]; rank 0 decides."""
@@ -256,7 +293,7 @@ class DistributedDataParallel(nn.Module):
                     g.record_stream(self._side_stream)
             b.table.bind(grads, self._side_stream)
             coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
-                        max_blocks=self.max_comm_blocks)
+                        max_blocks=self.max_comm_blocks, stage_base=b.stage_base, in_place=b.views is not None)
         else:
             # gloo / NCCL path: flat bucket, pre-scale, async all-reduce (what torch's Reducer does)
             flat = torch.cat([g.reshape(-1) for g in grads])
@@ -272,6 +309,14 @@ class DistributedDataParallel(nn.Module):
             return
         if self._use_kernels:
             torch.cuda.current_stream(self.device).wait_stream(self._side_stream)
+            for b in self._buckets:
+                if b.views is None:
+                    continue
+                # the reduced gradients are in the arena: point .grad at them (no copy back)
+                for view, j in zip(b.views, b.param_ids):
+                    p = self._params[j]
+                    if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                        p.grad = view
         else:
             for b in self._buckets:
                 if b.work is None:

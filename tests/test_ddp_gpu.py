@@ -46,6 +46,29 @@ def _collectives(rank, world, port, out_dir):
                 for a, b in zip(ts, ref):
                     err = (a - b).abs().max().item()
                     assert err <= tol * max(1.0, b.abs().max().item()), (mode, wire_bf16, a.numel(), err)
+    # tensors living in the arena: in-place two-shot, resident and stray tensors mixed
+    for rep in range(3):
+        numels = [3, 1000, 70001, 1_000_000]
+        table = coll.TensorTable(numels, dev, False, False)
+        views = coll.stage_views(arena, table, [(n,) for n in numels], stage_base=1 << 20)
+        stray = torch.randn(numels[1], device=dev)                 # not resident: copied in, left untouched
+        srcs = [torch.randn(n, device=dev) for n in numels]
+        srcs[1] = stray.clone()
+        for v, s_ in zip(views, srcs):
+            v.copy_(s_)
+        ref = [t.clone() for t in srcs]
+        for r in ref:
+            dist.all_reduce(r)
+            r.div_(world)
+        bound = [views[0], stray, views[2], views[3]]
+        table.bind(bound, torch.cuda.current_stream(dev))
+        mode = "nvls" if arena.has_multicast else "twoshot"
+        coll.launch(mode, arena, table, 1.0 / world, torch.cuda.current_stream(dev), stage_base=1 << 20, in_place=True)
+        torch.cuda.synchronize(dev)
+        arena.check_status()
+        for v, b in zip(views, ref):                               # results are read from the views
+            assert (v - b).abs().max().item() <= 1e-5 * max(1.0, b.abs().max().item())
+        assert torch.equal(stray, srcs[1])
     # results must be bit-identical on every rank (fixed summation order)
     t = torch.randn(100_003, device=dev)
     coll.all_reduce_([t], arena, mode="twoshot")
@@ -79,7 +102,7 @@ def test_fused_collectives_match_nccl(tmp_path):
     assert all((tmp_path / f"ok{r}").exists() for r in range(w))
 
 
-def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype):
+def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype, views=False):
     from pytorch_distributed_training_tutorials_b200.parallel.ddp import DistributedDataParallel as DDP
     st = group.init(backend="nccl", rank=rank, world_size=world, master_addr="127.0.0.1", master_port=port)
     dev = st.device
@@ -89,7 +112,8 @@ def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype):
         torch.manual_seed(5)
         return torch.nn.Sequential(torch.nn.Linear(64, 512), torch.nn.ReLU(), torch.nn.Linear(512, 2048),
                                    torch.nn.ReLU(), torch.nn.BatchNorm1d(2048), torch.nn.Linear(2048, 10)).to(dev)
-    mine = DDP(make(), device_ids=[dev.index], allreduce=mode, comm_dtype=comm_dtype, bucket_cap_mb=1)
+    mine = DDP(make(), device_ids=[dev.index], allreduce=mode, comm_dtype=comm_dtype, bucket_cap_mb=1,
+               gradient_as_bucket_view=views)
     ref = torch.nn.parallel.DistributedDataParallel(make(), device_ids=[dev.index], bucket_cap_mb=1)
     o1 = torch.optim.SGD(mine.parameters(), lr=0.05); o2 = torch.optim.SGD(ref.parameters(), lr=0.05)
     g = torch.Generator(device="cpu").manual_seed(11 + rank)
@@ -108,6 +132,21 @@ def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype):
     info = mine.get_logging_data()
     assert info["comm"] == "b200dt-peer-memory", info
     assert info["rebuilt"] and len(info["bucket_sizes_mib"]) > 1
+    if views:
+        # every gradient is a view of the symmetric arena, at the slot its bucket assigns
+        lo = mine._arena.buf.data_ptr(); hi = lo + mine._arena.nbytes
+        assert all(lo <= p.grad.data_ptr() < hi for p in mine.module.parameters())
+        assert all(m == "twoshot" or m == "nvls" for m in info["bucket_modes"])
+        # gradient accumulation under no_sync keeps adding into the views
+        x = torch.randn(32, 64, generator=g).to(dev); y = torch.randn(32, 10, generator=g).to(dev)
+        for m, o in ((mine, o1), (ref, o2)):
+            o.zero_grad()
+            with m.no_sync():
+                torch.nn.functional.mse_loss(m(x), y).backward()
+            torch.nn.functional.mse_loss(m(x), y).backward()
+            o.step()
+        for (n, p), q in zip(mine.module.named_parameters(), ref.module.parameters()):
+            assert torch.allclose(p, q, atol=tol, rtol=tol), (n, (p - q).abs().max().item())
     group.destroy()
     open(os.path.join(out_dir, f"ok{rank}"), "w").write(str(info["bucket_modes"]))
 
@@ -117,4 +156,54 @@ def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype):
 def test_ddp_matches_torch_ddp(tmp_path, mode, comm_dtype):
     w = _world()
     spawn(_ddp_vs_torch, args=(w, group.find_free_port(), str(tmp_path), mode, comm_dtype), nprocs=w)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(w))
+
+
+def _ddp_views_native(rank, world, port, out_dir):
+    """Own tcgen05 Linear layers: the weight-gradient GEMM writes straight into the arena slot."""
+    import pytorch_distributed_training_tutorials_b200 as b2
+    from pytorch_distributed_training_tutorials_b200.models.toy import MLP
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    st = group.init(backend="nccl", rank=rank, world_size=world, master_addr="127.0.0.1", master_port=port)
+    dev = st.device
+    models, opts = [], []
+    for views in (False, True):
+        torch.manual_seed(3)
+        m = b2.DistributedDataParallel(MLP(64, 256, 3, 16).to(dev), device_ids=[dev.index], bucket_cap_mb=0.25,
+                                       gradient_as_bucket_view=views)
+        models.append(m); opts.append(b2.FusedSGD(m.parameters(), lr=0.05))
+    g = torch.Generator(device="cpu").manual_seed(21 + rank)
+    for it in range(5):
+        x = torch.randn(64, 64, generator=g).to(dev); y = torch.randn(64, 16, generator=g).to(dev)
+        for m, o in zip(models, opts):
+            o.zero_grad()
+            Fn.mse_loss(m(x), y).backward()
+            o.step()
+    lo = models[1]._arena.buf.data_ptr(); hi = lo + models[1]._arena.nbytes
+    for (n, p), q in zip(models[1].module.named_parameters(), models[0].module.parameters()):
+        assert lo <= p.grad.data_ptr() < hi, n
+        assert torch.allclose(p, q, atol=1e-6, rtol=1e-5), (n, (p - q).abs().max().item())
+    # the 2-D weights' gradients were produced in place: after zero_grad + backward (no finalize yet
+    # needed to see it) their storage is the arena slot already
+    opts[1].zero_grad()
+    with models[1].no_sync():
+        Fn.mse_loss(models[1](x), y).backward()
+    w = models[1].module.layers[0].weight
+    assert lo <= w.grad.data_ptr() < hi
+    models[1].check_comm_status()
+    group.destroy()
+    open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+
+
+@needs2
+def test_ddp_gradient_views_with_native_layers(tmp_path):
+    w = _world()
+    spawn(_ddp_views_native, args=(w, group.find_free_port(), str(tmp_path)), nprocs=w)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(w))
+
+
+@needs2
+def test_ddp_gradient_as_bucket_view(tmp_path):
+    w = _world()
+    spawn(_ddp_vs_torch, args=(w, group.find_free_port(), str(tmp_path), "auto", "fp32", True), nprocs=w)
     assert all((tmp_path / f"ok{r}").exists() for r in range(w))

@@ -100,6 +100,12 @@ def test_data_parallel_virtual_devices_matches_chunked_reference(capsys):
             raise ValueError("bad replica")
     with pytest.raises(ValueError, match="replica"):
         DataParallel(Boom(), device_ids=["cpu", "cpu"])(x)
+    # in-order issue from the calling thread (the CUDA default) gives the same result and error surface
+    m.verbose = False
+    dp2 = DataParallel(m, device_ids=["cpu"] * 4, threaded=False)
+    assert torch.allclose(dp2(x), ref(x), atol=1e-6)
+    with pytest.raises(ValueError, match="replica 0"):
+        DataParallel(Boom(), device_ids=["cpu", "cpu"], threaded=False)(x)
 
 
 def test_checkpoint_roundtrip_with_plain_torch(tmp_path):
