@@ -54,11 +54,14 @@ def sweeps():
     out = ["# All-reduce sweep: fused peer-memory kernels (ours) vs NCCL 2.28.9", "",
            "`bench/allreduce_sweep.py`, CUDA events, max over ranks. Ours = ONE kernel doing gather -> scale -> (cast) -> reduce over",
            "NVLink peer memory -> scatter, on an ordinary (non-symmetric) tensor like NCCL's input. busbw = algbw * 2(N-1)/N.",
+           "`inplace` = the tensor lives in the symmetric arena (what DDP's gradient views use; like NCCL user-buffer registration):",
+           "no copy-in / copy-out, the reduce phase alone.",
            "NVLink roofline: 770 GB/s measured peer copy per direction per GPU (B200_PROFILING.md); the multicast (NVLS) path",
            "could not be exercised: torch's symmetric memory reports no multicast support on these boxes.", ""]
     for f in sorted(glob.glob(os.path.join(G, "allreduce_sweep_*.json"))):
         d = json.load(open(f)); n = d["world"]; fac = 2 * (n - 1) / n
-        keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_bf16wire_ms", "nvls_bf16wire_ms") if any(k in r for r in d["rows"])]
+        keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_inplace_ms", "nvls_inplace_ms",
+                            "twoshot_bf16wire_ms", "nvls_bf16wire_ms") if any(k in r for r in d["rows"])]
         out += [f"## {n} GPUs (multicast available: {d['multicast']})", "", "| bytes | " + " | ".join(k[:-3] + " us / busbw GB/s" for k in keys) + " |", "|---|" + "---|" * len(keys)]
         for r in d["rows"]:
             out.append(f"| {r['bytes']} | " + " | ".join((f"{r[k] * 1e3:.1f} / {r['bytes'] / (r[k] * 1e-3) * fac / 1e9:.1f}" if k in r else "-") for k in keys) + " |")
@@ -80,7 +83,7 @@ def benches():
 
 
 def misc():
-    for name in ("mp_bench.json", "toy_bench_dp_1.json", "toy_bench_dp_2.json", "toy_bench_ddp_2.json", "toy_bench_dp_8.json", "toy_bench_ddp_8.json", "conv_bench.json", "diag_gemm.json"):
+    for name in ("graphed_pipeline_bench.json", "pipeline_bench.json", "mp_bench.json", "toy_bench_dp_1.json", "toy_bench_dp_2.json", "toy_bench_ddp_2.json", "toy_bench_dp_8.json", "toy_bench_ddp_8.json", "conv_bench.json", "diag_gemm.json"):
         f = os.path.join(G, name)
         if os.path.exists(f):
             json.dump(json.load(open(f)), open(os.path.join(P, name), "w"), indent=1)
@@ -88,6 +91,27 @@ def misc():
         f = os.path.join(G, name)
         if os.path.exists(f):
             open(os.path.join(P, name.replace(".log", ".md")), "w").write("".join(l for l in open(f) if l.startswith("|")))
+    for name in ("ddp_overhead_2.txt", "ddp_overhead_8.txt"):
+        f = os.path.join(G, name)
+        if os.path.exists(f):
+            open(os.path.join(P, name), "w").write(open(f).read())
+    f = os.path.join(G, "graphed_pipeline_bench.json")
+    if os.path.exists(f):
+        d = json.load(open(f))
+        out = [f"# ResNet-50 split over 2 GPUs, mini-batch {d['batch']} at {d['size']}x{d['size']}: naive vs pipelined (BASELINE config 4)", "",
+               "`bench/graphed_pipeline_bench.py`: zero_grad + forward + loss + backward + SGD per step, device-timed on both GPUs.",
+               "`graphed` = every (stage, micro-batch) replayed from CUDA graphs (`parallel/graphed_pipeline.py`).", "",
+               "| variant | ms/step | img/s |", "|---|---|---|"]
+        for k, v in d.items():
+            if k.endswith("_ms"):
+                out.append(f"| {k[:-3]} | {v:.2f} | {d['batch'] / v * 1e3:.0f} |")
+        open(os.path.join(P, "pipeline_bench.md"), "w").write("\n".join(out) + "\n")
+    for name, title in (("launches_bs32.csv", "batch 32"),):
+        f = os.path.join(G, name)
+        if os.path.exists(f):
+            txt = subprocess.run([sys.executable, os.path.join(ROOT, "bench", "agg_launches.py"), f], capture_output=True, text=True).stdout
+            open(os.path.join(P, "launches_resnet50_step_bs32.md"), "w").write(
+                "# Same launch list at batch 32 (where the per-launch fixed costs show)\n\n```\n" + txt + "```\n")
 
 
 def ncu_reports():

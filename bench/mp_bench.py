@@ -97,7 +97,7 @@ def gpu_bound(res):
         m = ModelParallelResNet50(num_classes=num_classes); o = FusedSGD(m.parameters(), lr=1e-3)
         res["gpu_bound/ours_naive_mp"] = run(m, o, "cuda:1", Fn.mse_loss); del m, o
         for cut in ("layer2", "layer1"):
-            for split in (128, 256, 512):
+            for split in (256, 512):
                 m = PipelineParallelResNet50(split_size=split, num_classes=num_classes, split_after=cut); o = FusedSGD(m.parameters(), lr=1e-3)
                 res[f"gpu_bound/ours_pipelined_mp_cut_{cut}_split{split}"] = run(m, o, "cuda:1", Fn.mse_loss); del m, o
         m = ModelParallelResNet50(num_classes=num_classes, split_after="layer1"); o = FusedSGD(m.parameters(), lr=1e-3)
@@ -125,10 +125,29 @@ def main():
         m = ModelParallelResNet50(num_classes=num_classes); o = FusedSGD(m.parameters(), lr=1e-3)
         res["ours_naive_mp"] = timed(lambda: train_ours(m, "cuda:0", "cuda:1", o))
         del m, o
-        for split in (12, 20, 24, 30, 40, 60):
+        for split in (20, 40, 60):
             m = PipelineParallelResNet50(split_size=split, num_classes=num_classes); o = FusedSGD(m.parameters(), lr=1e-3)
             res[f"ours_pipelined_mp_split{split}"] = timed(lambda: train_ours(m, "cuda:0", "cuda:1", o))
             del m, o
+        # CUDA-graph replayed pipeline on the same workload (inputs still created on the host per batch)
+        from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+        idx = torch.LongTensor(batch_size).random_(0, num_classes).view(batch_size, 1)
+        for split in (30, 60):
+            m = PipelineParallelResNet50(split_size=split, num_classes=num_classes, split_after="layer1")
+            o = FusedSGD(m.parameters(), lr=1e-3)
+            ex_x = torch.randn(batch_size, 3, image_w, image_h, device="cuda:0")
+            ex_y = torch.zeros(batch_size, num_classes, device="cuda:1")
+            pipe = m.graphed(Fn.mse_loss, ex_x, ex_y)
+
+            def train_graphed():
+                for _ in range(num_batches):
+                    inputs = torch.randn(batch_size, 3, image_w, image_h)
+                    labels = torch.zeros(batch_size, num_classes).scatter_(1, idx, 1)
+                    pipe.zero_grad()
+                    pipe.train_step(inputs, labels)
+                    o.step()
+            res[f"ours_pipelined_graphed_cut_layer1_split{split}"] = timed(train_graphed)
+            del pipe, m, o
     ns = reference_cells()
     if ns is not None:
         import torchvision.models as models

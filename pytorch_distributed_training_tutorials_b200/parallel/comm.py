@@ -203,13 +203,91 @@ def broadcast_coalesced(tensors: Sequence[torch.Tensor], devices: Sequence[torch
                 df = torch.empty(total, dtype=dt, device=d)
             _wait_current(root, d)          # d's allocator may still have work queued on that block
             dst_flats.append(df)
-        with torch.cuda.device(root):
-            _lib.check(L.b200dt_p2p_broadcast(flat.data_ptr(), _lib.u64_array([f.data_ptr() for f in dst_flats]),
-                                              len(dst_flats), total * esz, _lib.stream_ptr(root)), "p2p_broadcast")
+        if len(dst_flats) >= 2 and total >= TWO_LEVEL_MIN_ELEMS:
+            _two_level_broadcast(flat, dst_flats, root)
+        else:
+            with torch.cuda.device(root):
+                _lib.check(L.b200dt_p2p_broadcast(flat.data_ptr(), _lib.u64_array([f.data_ptr() for f in dst_flats]),
+                                                  len(dst_flats), total * esz, _lib.stream_ptr(root)), "p2p_broadcast")
         for di, (d, df) in enumerate(zip(devices[1:], dst_flats), start=1):
             _wait_current(d, root)          # replicas on d start after the push has been issued & done
             for ti, t, o in zip(idxs, group, offs):
                 out[di][ti] = df[o:o + t.numel()].view(t.shape)
+    return out
+
+
+# Above this payload the root's NVLink port, not latency, bounds a root-centric broadcast / reduce
+# (N-1 copies of everything leave or enter ONE GPU); the two-level forms move (N-1)/N of the payload
+# through every port instead.
+TWO_LEVEL_MIN_ELEMS = 1 << 18
+
+
+def _slices(total: int, parts: int, align: int = 64):
+    per = -(-total // parts)
+    per = (per + align - 1) // align * align
+    out = []
+    for i in range(parts):
+        lo = min(total, i * per)
+        out.append((lo, min(total, lo + per)))
+    return out
+
+
+def _two_level_broadcast(flat: torch.Tensor, dst_flats: List[torch.Tensor], root: torch.device) -> None:
+    """Scatter + all-gather over NVSwitch: the root sends slice j only to peer j (one payload leaves
+    the root instead of N-1), then the peers exchange slices among themselves in N-2 rounds of
+    disjoint (source, destination) pairs.  Stream-ordered peer copies; no host synchronisation."""
+    m = len(dst_flats)
+    sl = _slices(flat.numel(), m)
+    with torch.cuda.device(root):
+        for j, df in enumerate(dst_flats):
+            lo, hi = sl[j]
+            if hi > lo:
+                df[lo:hi].copy_(flat[lo:hi], non_blocking=True)
+    for r in range(1, m):                       # round r: peer i hands its slice to peer (i + r) % m
+        for i in range(m):
+            j = (i + r) % m
+            lo, hi = sl[i]
+            if hi > lo:
+                with torch.cuda.device(dst_flats[i].device):
+                    dst_flats[j][lo:hi].copy_(dst_flats[i][lo:hi], non_blocking=True)
+
+
+def _two_level_reduce(flats: List[torch.Tensor], devs: List[torch.device], root: torch.device) -> torch.Tensor:
+    """Reduce-scatter + gather: device d sums slice d of every replica's flat gradient with the pull
+    kernel (its own port carries (N-1)/N of one payload), the root then collects the reduced slices."""
+    n = len(flats)
+    total = flats[0].numel()
+    sl = _slices(total, n)
+    L = _lib.lib()
+    with torch.cuda.device(root):
+        out = torch.empty(total, dtype=torch.float32, device=root)
+    ri = next((i for i, d in enumerate(devs) if d == root), None)
+    parts = []
+    for d in range(n):
+        lo, hi = sl[d]
+        if hi <= lo:
+            parts.append(None)
+            continue
+        for k in range(n):
+            if k != d:
+                _wait_current(devs[d], devs[k])          # everybody's flat gradient is complete
+        with torch.cuda.device(devs[d]):
+            dst = out[lo:hi] if d == ri else torch.empty(hi - lo, dtype=torch.float32, device=devs[d])
+            if d == ri:
+                _wait_current(devs[d], root)
+            _lib.check(L.b200dt_p2p_reduce_f32(dst.data_ptr(), _lib.u64_array([f.data_ptr() + lo * 4 for f in flats]),
+                                               n, hi - lo, 1.0, 0, _lib.stream_ptr(devs[d])), "p2p_reduce")
+        parts.append(dst)
+    with torch.cuda.device(root):
+        for d in range(n):
+            if parts[d] is not None and d != ri:
+                lo, hi = sl[d]
+                out[lo:hi].copy_(parts[d], non_blocking=True)
+    # the sources must outlive the pulls issued on the other devices' streams
+    for d in range(n):
+        for k in range(n):
+            if k != d and flats[k].is_cuda:
+                flats[k].record_stream(torch.cuda.current_stream(devs[d]))
     return out
 
 
@@ -247,13 +325,16 @@ def reduce_add_coalesced(per_device_grads: List[List[Optional[torch.Tensor]]], r
             flats.append(torch.cat([per_device_grads[d][i].reshape(-1) for i in active]))
         _wait_current(root, devs[d])
     total = flats[0].numel()
-    with torch.cuda.device(root):
-        out = torch.empty(total, dtype=torch.float32, device=root)
-        _lib.check(_lib.lib().b200dt_p2p_reduce_f32(out.data_ptr(), _lib.u64_array([f.data_ptr() for f in flats]),
-                                                    ndev, total, 1.0, 0, _lib.stream_ptr(root)), "p2p_reduce")
-    for d in range(ndev):
-        if devs[d] != root:
-            flats[d].record_stream(torch.cuda.current_stream(root))
+    if ndev >= 3 and total >= TWO_LEVEL_MIN_ELEMS and len(set(devs)) == ndev and root in devs:
+        out = _two_level_reduce(flats, devs, root)
+    else:
+        with torch.cuda.device(root):
+            out = torch.empty(total, dtype=torch.float32, device=root)
+            _lib.check(_lib.lib().b200dt_p2p_reduce_f32(out.data_ptr(), _lib.u64_array([f.data_ptr() for f in flats]),
+                                                        ndev, total, 1.0, 0, _lib.stream_ptr(root)), "p2p_reduce")
+        for d in range(ndev):
+            if devs[d] != root:
+                flats[d].record_stream(torch.cuda.current_stream(root))
     off = 0
     for i in active:
         g = per_device_grads[0][i]

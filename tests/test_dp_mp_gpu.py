@@ -65,6 +65,32 @@ def test_data_parallel_batchnorm_buffers_and_big_model():
     assert int(m[1].num_batches_tracked) == 1
 
 
+@pytest.mark.skipif(_ngpu() < 3, reason="the two-level broadcast / reduce needs >= 3 GPUs")
+def test_data_parallel_two_level_transfers_match_torch():
+    """>= 3 devices and >= 1 MB of parameters: scatter + all-gather broadcast, reduce-scatter + gather."""
+    from pytorch_distributed_training_tutorials_b200.parallel.data_parallel import DataParallel
+    from pytorch_distributed_training_tutorials_b200.parallel import comm
+    n = min(_ngpu(), 8)
+    torch.manual_seed(4)
+    m = torch.nn.Sequential(torch.nn.Linear(96, 1024), torch.nn.ReLU(), torch.nn.Linear(1024, 1000), torch.nn.ReLU(),
+                            torch.nn.Linear(1000, 5)).to("cuda:0")
+    assert sum(p.numel() for p in m.parameters()) >= comm.TWO_LEVEL_MIN_ELEMS
+    r = copy.deepcopy(m)
+    mine = DataParallel(m, device_ids=list(range(n))); ref = torch.nn.DataParallel(r, device_ids=list(range(n)))
+    o1 = torch.optim.SGD(m.parameters(), lr=0.05); o2 = torch.optim.SGD(r.parameters(), lr=0.05)
+    for it in range(4):
+        x = torch.randn(16 * n, 96, device="cuda:0"); y = torch.randn(16 * n, 5, device="cuda:0")
+        o1.zero_grad(); F.mse_loss(mine(x), y).backward(); o1.step()
+        o2.zero_grad(); F.mse_loss(ref(x), y).backward(); o2.step()
+    for p, q in zip(m.parameters(), r.parameters()):
+        assert torch.allclose(p, q, atol=2e-5, rtol=1e-4), (p - q).abs().max()
+    # the replicas really received the parameters (not just replica 0)
+    reps = comm.broadcast_coalesced([p.detach() for p in m.parameters()], [torch.device("cuda", i) for i in range(n)])
+    for d in range(1, n):
+        for a, b in zip(reps[d], m.parameters()):
+            assert a.device.index == d and torch.equal(a.cpu(), b.detach().cpu())
+
+
 @needs2
 def test_toy_model_parallel_and_multi_device_optimizer():
     from pytorch_distributed_training_tutorials_b200.models.toy import ToyModel
