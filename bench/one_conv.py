@@ -1,5 +1,5 @@
 """Run one conv shape a few times (for ncu --set full on tc_gemm_kernel).
-usage: one_conv.py NB H Cin Cout R stride [fprop|dgrad|wgrad]"""
+usage: one_conv.py NB H Cin Cout R stride [fprop|dgrad|dgrad_acc|wgrad]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -10,7 +10,9 @@ dev = torch.device("cuda:0")
 x = torch.randn(NB, H, H, Cin, device=dev).bfloat16()
 w = (torch.randn(Cout, R, R, Cin, device=dev) * 0.05).bfloat16()
 dy = torch.randn(NB, H // s, H // s, Cout, device=dev).bfloat16()
+acc = torch.randn(NB, H, H, Cin, device=dev).bfloat16()
 fn = {"fprop": lambda: NV.conv2d_fprop(x, w, stride=s), "dgrad": lambda: NV.conv2d_dgrad(dy, w, x.shape, R, stride=s),
+      "dgrad_acc": lambda: NV.conv2d_dgrad(dy, w, x.shape, R, stride=s, accumulate_into=acc),
       "wgrad": lambda: NV.conv2d_wgrad(x, dy, R, stride=s)}[what]
 for _ in range(5):
     fn()
