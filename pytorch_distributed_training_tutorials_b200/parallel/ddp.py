@@ -20,6 +20,7 @@ Same construction-time and per-step contract as the wrapper the reference uses a
 from __future__ import annotations
 
 import contextlib
+import os
 import sys
 import time
 from typing import List, Optional
@@ -29,6 +30,7 @@ import torch.distributed as dist
 from torch import nn
 
 from .. import group as _group
+from ..utils.timing import trace_range
 from ._native_reducer import load as _load_reducer
 
 FIRST_BUCKET_BYTES = 1024 * 1024
@@ -70,6 +72,11 @@ class DistributedDataParallel(nn.Module):
         self.comm_dtype = comm_dtype
         self.max_comm_blocks = max_comm_blocks
         self.gradient_as_bucket_view = gradient_as_bucket_view
+        # B200DT_DEBUG=1: before every bucket collective all ranks compare (sequence number, bucket
+        # index, byte size); a rank that issues collectives in another order raises instead of
+        # hanging in a flag barrier (the role ProcessGroupWrapper plays for torch's DDP)
+        self._debug = os.environ.get("B200DT_DEBUG", "0") not in ("", "0")
+        self._debug_seq = 0
 
         self._params = [p for p in module.parameters() if p.requires_grad]
         if not self._params:
@@ -270,6 +277,19 @@ class DistributedDataParallel(nn.Module):
         self._rebuilt = True
         self._stats["rebuilds"] += 1
 
+    def _debug_handshake(self, bi: int, b: "_Bucket") -> None:
+        if self.device.type == "cuda" and torch.cuda.is_current_stream_capturing():
+            return                                    # host round trips cannot be captured
+        self._debug_seq += 1
+        dev = self.device if dist.get_backend(self.process_group) == "nccl" else torch.device("cpu")
+        mine = torch.tensor([self._debug_seq, bi, b.nbytes], dtype=torch.int64, device=dev)
+        allv = [torch.zeros_like(mine) for _ in range(self.world_size)]
+        dist.all_gather(allv, mine, group=self.process_group)
+        for r, v in enumerate(allv):
+            if not torch.equal(v.cpu(), mine.cpu()):
+                raise RuntimeError(f"collective mismatch: rank {self.rank} is at (seq, bucket, bytes)={mine.tolist()} "
+                                   f"but rank {r} is at {v.tolist()}")
+
     # ------------------------------------------------------------------ reducer callbacks
     def _on_bucket_ready(self, bi: int) -> None:
         b = self._buckets[bi]
@@ -283,6 +303,8 @@ class DistributedDataParallel(nn.Module):
             grads.append(g if g.is_contiguous() else g.contiguous())
         self._stats["allreduce_bytes"] += b.nbytes
         self._stats["launches"] += 1
+        if self._debug:
+            self._debug_handshake(bi, b)
         if self._use_kernels:
             from ..ops import collectives as coll
             cur = torch.cuda.current_stream(self.device)
@@ -292,8 +314,9 @@ class DistributedDataParallel(nn.Module):
                 for g in grads:
                     g.record_stream(self._side_stream)
             b.table.bind(grads, self._side_stream)
-            coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
-                        max_blocks=self.max_comm_blocks, stage_base=b.stage_base, in_place=b.views is not None)
+            with trace_range(f"allreduce[{bi}]"):
+                coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
+                            max_blocks=self.max_comm_blocks, stage_base=b.stage_base, in_place=b.views is not None)
         else:
             # gloo / NCCL path: flat bucket, pre-scale, async all-reduce (what torch's Reducer does)
             flat = torch.cat([g.reshape(-1) for g in grads])

@@ -17,6 +17,28 @@ import torch.nn.functional as F
 from torch.utils.data import DataLoader
 
 
+from .utils.timing import trace_range
+
+
+def _parse_fault(spec: str):
+    """``B200DT_FAULT_INJECT="rank=1,step=3"``: that rank raises at that global step (tests of the
+    launchers' failure handling: the first failing child is reported, its siblings are killed)."""
+    if not spec:
+        return None
+    kv = dict(item.split("=") for item in spec.replace(" ", "").split(",") if "=" in item)
+    try:
+        return int(kv["rank"]), int(kv["step"])
+    except (KeyError, ValueError):
+        raise ValueError(f"B200DT_FAULT_INJECT must look like 'rank=R,step=S', got {spec!r}")
+
+
+def _current_rank() -> int:
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank()
+    return int(os.environ.get("RANK", "0"))
+
+
 def default_loss(output: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
     """``F.cross_entropy`` as the reference calls it (ddp_gpus.py:37); on CUDA the fused kernel."""
     if output.is_cuda and output.dtype in (torch.float32, torch.bfloat16):
@@ -43,6 +65,7 @@ class Trainer:
         self.global_step = 0
         self.cuda_graph = cuda_graph and self.device.type == "cuda"
         self._graphed = None
+        self._fault = _parse_fault(os.environ.get("B200DT_FAULT_INJECT", ""))
         if wrap_ddp:
             from .parallel.ddp import DistributedDataParallel
             ids = [gpu_id] if self.device.type == "cuda" else None
@@ -55,6 +78,8 @@ class Trainer:
             self.cuda_graph = False
 
     def _run_batch(self, xs, ys):
+        if self._fault is not None and self._fault == (_current_rank(), self.global_step):
+            raise RuntimeError(f"fault injected on rank {self._fault[0]} at step {self._fault[1]} (B200DT_FAULT_INJECT)")
         if self.cuda_graph:
             if self._graphed is None:
                 from .utils.graph import GraphedTrainStep
@@ -64,10 +89,13 @@ class Trainer:
                 self.global_step += 1
                 return self.last_loss
         self.optimizer.zero_grad()
-        output = self.model(xs)
-        loss = self.loss_fn(output, ys)
-        loss.backward()
-        self.optimizer.step()
+        with trace_range("forward"):
+            output = self.model(xs)
+            loss = self.loss_fn(output, ys)
+        with trace_range("backward"):
+            loss.backward()
+        with trace_range("optimizer.step"):
+            self.optimizer.step()
         self.last_loss = loss.detach()
         self.global_step += 1
         return self.last_loss

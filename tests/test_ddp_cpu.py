@@ -123,3 +123,44 @@ def test_ddp_detects_shape_mismatch():
     with pytest.raises(ProcessRaisedException) as ei:
         spawn(_mismatch, args=(2, _find_port()), nprocs=2)
     assert "same model across all ranks" in str(ei.value)
+
+
+def _fault_injected_trainer(rank, world, port):
+    """Trainer under DDP with B200DT_FAULT_INJECT: rank 1 dies at global step 2; with B200DT_DEBUG the
+    bucket handshake runs before every all-reduce; with B200DT_TRACE the ranges are recorded."""
+    os.environ["B200DT_FAULT_INJECT"] = "rank=1,step=2"
+    os.environ["B200DT_DEBUG"] = "1"
+    _setup(rank, world, port)
+    from torch.utils.data import DataLoader
+    ds = b2.MyTrainDataset(64)
+    loader = DataLoader(ds, batch_size=8, shuffle=False, sampler=b2.DistributedSampler(ds))
+    model = torch.nn.Linear(20, 1)
+    tr = b2.Trainer(model, loader, torch.optim.SGD(model.parameters(), lr=0.01), gpu_id=rank,
+                    loss_fn=torch.nn.functional.mse_loss)
+    assert tr.model._debug
+    tr.train(2)             # 4 steps per epoch: the fault fires in the first epoch
+    group.destroy()
+
+
+def test_fault_injection_is_reported_with_rank_and_siblings_are_torn_down():
+    with pytest.raises(ProcessRaisedException) as ei:
+        spawn(_fault_injected_trainer, args=(2, _find_port()), nprocs=2)
+    assert ei.value.rank == 1 and "fault injected on rank 1 at step 2" in str(ei.value)
+
+
+def _handshake_mismatch(rank, world, port):
+    os.environ["B200DT_DEBUG"] = "1"
+    _setup(rank, world, port)
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 8), torch.nn.Linear(8, 1))
+    ddp = DDP(model)
+    # desynchronise the ranks on purpose: rank 1 believes it already issued one more collective
+    if rank == 1:
+        ddp._debug_seq += 1
+    torch.nn.functional.mse_loss(ddp(torch.randn(4, 8)), torch.randn(4, 1)).backward()
+
+
+def test_debug_handshake_catches_desynchronised_collectives():
+    with pytest.raises(ProcessRaisedException) as ei:
+        spawn(_handshake_mismatch, args=(2, _find_port()), nprocs=2)
+    assert "collective mismatch" in str(ei.value)
