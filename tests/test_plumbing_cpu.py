@@ -279,3 +279,54 @@ def test_trainer_run_batches_cpu_matches_manual_loop():
     assert tr.global_step == 4
     for p, q in zip(m.parameters(), r.parameters()):
         assert torch.allclose(p, q)
+
+
+# --------------------------------------------------------------------------- multi-node emulation, busy port
+def test_two_launcher_agents_emulate_two_nodes(tmp_path):
+    """``--nnodes 2`` with two agents on one host (different --node-rank, shared master port): ranks
+    0 and 1 meet over gloo and all-reduce."""
+    from pytorch_distributed_training_tutorials_b200 import group
+    script = tmp_path / "n.py"
+    script.write_text(
+        "import os, torch, torch.distributed as dist\n"
+        "import pytorch_distributed_training_tutorials_b200 as b2\n"
+        "st = b2.init(backend='gloo')\n"
+        "t = torch.tensor([float(st.rank + 1)]); dist.all_reduce(t)\n"
+        f"open(r'{tmp_path}' + '/r' + str(st.rank), 'w').write(f\"{{st.world_size}} {{os.environ['GROUP_RANK']}} {{os.environ['LOCAL_RANK']}} {{t.item()}}\")\n"
+        "b2.destroy()\n")
+    port = group.find_free_port()
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    base = [sys.executable, "-m", "pytorch_distributed_training_tutorials_b200.run", "--nnodes", "2", "--nproc-per-node", "1",
+            "--master-addr", "127.0.0.1", "--master-port", str(port)]
+    procs = [subprocess.Popen(base + ["--node-rank", str(nr), str(script)], env=env, stdout=subprocess.PIPE,
+                              stderr=subprocess.PIPE, text=True) for nr in (0, 1)]
+    for p in procs:
+        out, err = p.communicate(timeout=180)
+        assert p.returncode == 0, err
+    assert (tmp_path / "r0").read_text() == "2 0 0 3.0"
+    assert (tmp_path / "r1").read_text() == "2 1 0 3.0"
+
+
+def _busy_port_child(rank, port):
+    from pytorch_distributed_training_tutorials_b200 import group
+    group.init(backend="gloo", rank=0, world_size=1, master_addr="127.0.0.1", master_port=port, timeout_s=20)
+
+
+def test_busy_master_port_is_an_error_not_a_hang():
+    """The reference hard-codes port 12345, so a stale run makes the next one collide
+    (/root/reference/ddp_gpus.py:14); here the collision surfaces as an exception naming the problem,
+    and ``find_free_port`` / the launcher's default avoid it in the first place."""
+    import socket
+    from pytorch_distributed_training_tutorials_b200 import group
+    from pytorch_distributed_training_tutorials_b200.launch.spawn import spawn, ProcessRaisedException
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); s.listen(1)
+    port = s.getsockname()[1]
+    try:
+        with pytest.raises(ProcessRaisedException) as ei:
+            spawn(_busy_port_child, args=(port,), nprocs=1)
+        msg = str(ei.value).lower()
+        assert "address already in use" in msg or "eaddrinuse" in msg or "in use" in msg, msg
+    finally:
+        s.close()
+    p1, p2 = group.find_free_port(), group.find_free_port()
+    assert 1024 < p1 < 65536 and 1024 < p2 < 65536
