@@ -42,7 +42,20 @@ def resnet() -> None:
     pp = PipelineParallelResNet50(split_size=20, num_classes=1000)
     x = torch.randn(120, 3, 128, 128)
     print("naive:", tuple(mp(x).shape), "pipelined:", tuple(pp(x).shape))
-    print("timings: python bench/mp_bench.py")
+    # the fast pipelined form: every (stage, micro-batch) is captured once and replayed from CUDA graphs
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD
+    gp = PipelineParallelResNet50(split_size=60, num_classes=1000, split_after="layer1")
+    opt = FusedSGD(gp.parameters(), lr=1e-3)
+    labels = torch.zeros(120, 1000).scatter_(1, torch.randint(0, 1000, (120, 1)), 1)
+    pipe = gp.graphed(Fn.mse_loss, x.to(gp.dev0), labels.to(gp.dev1))
+    for _ in range(3):
+        pipe.zero_grad()
+        loss = pipe.train_step(x, labels)
+        opt.step()
+    print(f"graph-replayed pipeline ({pipe.chunks} micro-batches, {pipe.launches_per_step} graph launches per step): "
+          f"loss {float(loss):.4f}")
+    print("timings: python bench/mp_bench.py ; python bench/graphed_pipeline_bench.py")
 
 
 def place(cpu: bool) -> None:
