@@ -76,6 +76,17 @@ def main():
             opt.zero_grad(); Fn.mse_loss(dp(x), y).backward(); opt.step()
         ms = timed(step_mine, args.steps, args.warmup, dev, False)
         res["ours_ms"] = ms; res["ours_samples_per_s"] = B / ms * 1e3
+        if n > 1:
+            # persistent replicas + one CUDA graph per device (parallel/graphed_data_parallel.py)
+            gm = MLP(IN, HID, DEPTH, OUT).to(dev)
+            gopt = b2.FusedSGD(gm.parameters(), lr=1e-4)
+            gdp = b2.GraphedDataParallel(gm, ids, Fn.mse_loss, x, y)
+
+            def step_graphed():
+                gopt.zero_grad(); gdp.train_step(x, y); gopt.step()
+            ms = timed(step_graphed, args.steps, args.warmup, dev, False)
+            res["ours_graphed_ms"] = ms; res["ours_graphed_samples_per_s"] = B / ms * 1e3
+            del gdp, gm, gopt
         ref_m = Autocast(torch_mlp()).to(dev)
         rdp = nn.DataParallel(ref_m, device_ids=ids) if n > 1 else ref_m
         ropt = torch.optim.SGD(ref_m.parameters(), lr=1e-4)

@@ -21,6 +21,7 @@ _LAZY = {
     "DistributedDataParallel": ("parallel.ddp", "DistributedDataParallel"),
     "DataParallel": ("parallel.data_parallel", "DataParallel"),
     "GraphedPipeline": ("parallel.graphed_pipeline", "GraphedPipeline"),
+    "GraphedDataParallel": ("parallel.graphed_data_parallel", "GraphedDataParallel"),
     "PipelineStage": ("parallel.pipeline", "PipelineStage"),
     "Trainer": ("trainer", "Trainer"),
     "save_checkpoint": ("checkpoint", "save_checkpoint"),

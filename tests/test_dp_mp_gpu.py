@@ -163,3 +163,42 @@ def test_auto_place_dispatch_runs_across_devices():
     assert torch.allclose(out.cpu(), ref(ids).cpu(), atol=1e-4)
     out.float().mean().backward()
     assert all(p.grad is not None for p in m.parameters())
+
+
+@needs2
+def test_graphed_data_parallel_matches_single_device_training():
+    """Persistent replicas + one CUDA graph per device: same losses and parameters as training the
+    whole mini-batch on one GPU (mean-reduced loss), including the per-step state broadcast."""
+    import pytorch_distributed_training_tutorials_b200 as b2
+    from pytorch_distributed_training_tutorials_b200.models.toy import MLP
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    n = min(_ngpu(), 4)
+    torch.manual_seed(6)
+    m = MLP(in_features=64, hidden=256, depth=3, out_features=16).to("cuda:0")
+    r = copy.deepcopy(m)
+    o = b2.FusedSGD(m.parameters(), lr=0.05); ro = b2.FusedSGD(r.parameters(), lr=0.05)
+    B = 32 * n
+    x = torch.randn(B, 64, device="cuda:0"); y = torch.randn(B, 16, device="cuda:0")
+    gdp = b2.GraphedDataParallel(m, list(range(n)), Fn.mse_loss, x, y)
+    assert gdp.launches_per_step == n
+    got, ref = [], []
+    for it in range(5):
+        torch.manual_seed(50 + it)
+        xb = torch.randn(B, 64, device="cuda:0"); yb = torch.randn(B, 16, device="cuda:0")
+        o.zero_grad()                                   # set_to_none: the flat views must be re-attached
+        got.append(float(gdp.train_step(xb, yb)))
+        o.step()
+        ro.zero_grad()
+        l = Fn.mse_loss(r(xb), yb); l.backward(); ro.step()
+        ref.append(float(l))
+    for a, b in zip(got, ref):
+        assert abs(a - b) <= 2e-3 * abs(b) + 1e-5, (got, ref)
+    for p, q in zip(m.parameters(), r.parameters()):
+        assert torch.allclose(p, q, rtol=2e-3, atol=2e-4), (p - q).abs().max()
+    # replicas carry the root's current parameters after the next broadcast
+    gdp.train_step(xb, yb)
+    for d in range(1, n):
+        for p0, pd in zip(m.parameters(), gdp.replicas[d].parameters()):
+            assert pd.device.index == d
+    with pytest.raises(ValueError):
+        gdp.train_step(xb[:8], yb[:8])
