@@ -330,3 +330,65 @@ def test_busy_master_port_is_an_error_not_a_hang():
         s.close()
     p1, p2 = group.find_free_port(), group.find_free_port()
     assert 1024 < p1 < 65536 and 1024 < p2 < 65536
+
+
+# --------------------------------------------------------------------------- small pure-Python helpers
+def test_two_level_slices_cover_the_range_exactly():
+    from pytorch_distributed_training_tutorials_b200.parallel.comm import _slices
+    for total in (0, 1, 63, 64, 65, 1000, 262144, 67_000_003):
+        for parts in (1, 2, 3, 7, 8):
+            sl = _slices(total, parts)
+            assert len(sl) == parts
+            covered = 0
+            for lo, hi in sl:
+                assert lo == covered or (lo == total and hi == total)
+                assert lo % 64 == 0 or lo == total
+                covered = max(covered, hi)
+            assert covered == total
+
+
+def test_tensor_table_stage_layout_is_contiguous_per_tensor():
+    """Every tensor of a bucket occupies one contiguous, 32-byte aligned range of the staging region:
+    that is what lets DDP hand out gradient VIEWS of the arena (in-place all-reduce)."""
+    from pytorch_distributed_training_tutorials_b200.ops.collectives import TensorTable
+    numels = [3, 1000, 70001, 16384, 1, 2_000_003]
+    for blocks in (4, 32, 128):
+        t = TensorTable(numels, torch.device("cpu"), False, False, target_blocks=blocks)
+        assert len(t.tensor_offsets) == len(numels)
+        end = 0
+        for off, n in zip(t.tensor_offsets, numels):
+            assert off % 8 == 0 and off >= end
+            end = off + n
+        assert t.stage_elems >= end and t.stage_bytes == t.stage_elems * 4
+        raw = t.chunks.view(-1, 3)
+        # chunk rows: (start << 32 | tensor, len, stage_off); a tensor's chunks follow each other in the stage
+        per_tensor = {}
+        for row in raw.tolist():
+            ti, start = row[0] & 0xFFFFFFFF, row[0] >> 32
+            per_tensor.setdefault(ti, []).append((start, row[1] & 0xFFFFFFFF, row[2]))
+        for ti, rows in per_tensor.items():
+            base = t.tensor_offsets[ti]
+            for start, ln, off in rows:
+                assert off == base + start
+            assert sum(ln for _, ln, _ in rows) == numels[ti]
+
+
+def test_fault_spec_parsing():
+    from pytorch_distributed_training_tutorials_b200.trainer import _parse_fault
+    assert _parse_fault("") is None
+    assert _parse_fault("rank=1,step=3") == (1, 3)
+    assert _parse_fault(" step=0 , rank=7 ") == (7, 0)
+    with pytest.raises(ValueError):
+        _parse_fault("rank=1")
+    with pytest.raises(ValueError):
+        _parse_fault("rank=a,step=2")
+
+
+def test_graphed_wrappers_refuse_cpu_devices():
+    import pytorch_distributed_training_tutorials_b200 as b2
+    m = torch.nn.Linear(8, 2)
+    x, y = torch.randn(4, 8), torch.randn(4, 2)
+    with pytest.raises(ValueError, match="CUDA"):
+        b2.GraphedDataParallel(m, ["cpu", "cpu"], torch.nn.functional.mse_loss, x, y)
+    with pytest.raises(ValueError, match="CUDA"):
+        b2.GraphedPipeline([m], ["cpu"], 2, torch.nn.functional.mse_loss, x, y)
