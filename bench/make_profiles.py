@@ -26,7 +26,7 @@ def launches():
            "compare shares, not absolutes.", "", f"total kernel time {total / 1e6:.2f} ms over {sum(cnt.values())} launches", "",
            "| kernel | launches | ms | share |", "|---|---|---|---|"]
     for k, v in sorted(tot.items(), key=lambda kv: -kv[1])[:20]:
-        own = "b200::" in k or k.startswith(("filter_transpose", "zero_phase"))
+        own = "b200::" in k or k.startswith("zero_phase")
         out.append(f"| `{k}`{'' if own else ' (torch)'} | {cnt[k]} | {v / 1e6:.3f} | {100 * v / total:.1f}% |")
     open(os.path.join(P, "launches_resnet50_step.md"), "w").write("\n".join(out) + "\n")
 

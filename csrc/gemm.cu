@@ -1141,48 +1141,3 @@ extern "C" int b200dt_gemm_nn_bf16(const void* A, const void* B, void* C, int M,
   }
   return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
 }
-
-// Filter re-layout for the data gradient (see b200dt_conv2d_dgrad_bf16). w: [Cout,R,R,Cin] bf16,
-// wt: R*R*Cout*Cin bf16.
-__global__ void filter_transpose_kernel(const __nv_bfloat16* __restrict__ w,
-                                        __nv_bfloat16* __restrict__ wt, int Cin, int Cout, int R,
-                                        int stride) {
-  const int pad = R / 2;
-  const long long total = (long long)R * R * Cout * Cin;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    // i enumerates the destination: phases, then [Cin][tap][Cout]
-    long long rem = i;
-    int found = 0;
-    for (int py = 0; py < stride && !found; ++py)
-      for (int px = 0; px < stride && !found; ++px) {
-        int taps_r[9], taps_s[9], nt = 0;
-        for (int rr = 0; rr < R; ++rr)
-          for (int ss = 0; ss < R; ++ss)
-            if (((py + pad - rr) % stride == 0) && ((px + pad - ss) % stride == 0)) {
-              taps_r[nt] = rr; taps_s[nt] = ss; ++nt;
-            }
-        const long long sz = (long long)nt * Cout * Cin;
-        if (rem < sz) {
-          const int co = (int)(rem % Cout);
-          const int t = (int)((rem / Cout) % nt);
-          const int ci = (int)(rem / ((long long)Cout * nt));
-          wt[i] = w[(((long long)co * R + taps_r[t]) * R + taps_s[t]) * Cin + ci];
-          found = 1;
-        } else {
-          rem -= sz;
-        }
-      }
-  }
-}
-
-extern "C" int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R,
-                                            int stride, void* stream) {
-  const long long total = (long long)R * R * Cout * Cin;
-  int blocks = (int)((total + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  filter_transpose_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(w), reinterpret_cast<__nv_bfloat16*>(wt), Cin, Cout, R,
-      stride);
-  return (int)cudaGetLastError();
-}

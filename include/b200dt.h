@@ -47,8 +47,6 @@ int b200dt_conv2d_dgrad_bf16(const void* dy, const void* w, void* dx, int NB, in
  * written through a tensor map (caller then uses the plain entry point and adds). */
 int b200dt_conv2d_dgrad_acc_bf16(const void* dy, const void* w, void* dx, int NB, int H, int W,
                                  int Cin, int Cout, int R, int stride, void* stream);
-int b200dt_filter_transpose_bf16(const void* w, void* wt, int Cin, int Cout, int R, int stride,
-                                 void* stream);
 
 /* ---------------------------------------------------------------- layout / stem helpers
  * Replaces the cuDNN 7x7 stem convolution's gather (03.model_parallel.ipynb:812). csrc/layout.cu */

@@ -48,7 +48,6 @@ _SIGS = {
     "b200dt_conv2d_wgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_conv2d_dgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_conv2d_dgrad_acc_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
-    "b200dt_filter_transpose_bf16": [vp, vp, i32, i32, i32, i32, vp],
     "b200dt_stem_im2col": [vp, vp, i32, i32, i32, i32, vp],
     "b200dt_cast_f32_to_bf16": [vp, vp, i64, vp],
     "b200dt_transpose_bf16": [vp, vp, i32, i32, vp],

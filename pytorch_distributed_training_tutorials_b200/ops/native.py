@@ -123,16 +123,6 @@ def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, R: int, stride: int = 1,
     return out
 
 
-def filter_transpose(w: torch.Tensor, stride: int = 1) -> torch.Tensor:
-    _need(w, BF16, "w")
-    Cout, R, S, Cin = w.shape
-    wt = torch.empty(R * S * Cout * Cin, device=w.device, dtype=BF16)
-    with on_device(w.device):
-        check(lib().b200dt_filter_transpose_bf16(ptr(w), ptr(wt), Cin, Cout, R, stride,
-                                                 stream_ptr(w.device)), "filter_transpose")
-    return wt
-
-
 def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape, R: int, stride: int = 1,
                  accumulate_into: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Data gradient; ``w`` is the forward filter ``[Cout, R, R, Cin]`` (no transposed copy needed).
