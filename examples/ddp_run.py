@@ -6,7 +6,8 @@
 Rank, world size and rendezvous come from the environment (RANK / WORLD_SIZE / LOCAL_RANK /
 MASTER_ADDR / MASTER_PORT).  Launched without ``--nproc-per-node`` it runs ONE worker and 64 steps
 per epoch: the lesson of the reference's notebook (02.ddp_toy_example.ipynb:268-272).
-``--model mlp`` swaps in the tcgen05 MLP, ``--save ckpt.pt`` writes a rank-0 checkpoint per epoch.
+``--model mlp`` swaps in the tcgen05 MLP, ``--save ckpt.pt`` writes a rank-0 checkpoint per epoch,
+``--resume ckpt.pt`` loads one (on every rank, before wrapping) and continues with the next epoch.
 """
 import argparse
 import os
@@ -20,7 +21,7 @@ import pytorch_distributed_training_tutorials_b200 as b2
 from pytorch_distributed_training_tutorials_b200.trainer import Trainer
 
 
-def main(max_epochs: int, batch_size: int, backend, model_name: str, save: str):
+def main(max_epochs: int, batch_size: int, backend, model_name: str, save: str, resume: str = ""):
     st = b2.init(backend=backend)
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if model_name == "mlp":
@@ -37,9 +38,15 @@ def main(max_epochs: int, batch_size: int, backend, model_name: str, save: str):
         optimizer = torch.optim.SGD(model.parameters(), lr=1e-2)
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, pin_memory=st.device.type == "cuda",
                                   shuffle=False, sampler=b2.DistributedSampler(train_dataset))
+    start_epoch = 0
+    if resume:
+        info = b2.load_checkpoint(resume, model, optimizer)
+        start_epoch = info["epoch"] + 1
+        if st.rank == 0:
+            print(f"resumed from {resume}: continuing with epoch {start_epoch}")
     trainer = Trainer(model=model, optimizer=optimizer, train_dataloader=train_dataloader, gpu_id=local_rank,
                       loss_fn=loss_fn)
-    for epoch in range(max_epochs):
+    for epoch in range(start_epoch, max_epochs):
         trainer._run_epoch(epoch)
         if save:
             b2.save_checkpoint(trainer.model, optimizer, epoch, save)
@@ -53,5 +60,6 @@ if __name__ == "__main__":
     parser.add_argument("--backend", default=None)
     parser.add_argument("--model", default="linear", choices=["linear", "mlp"])
     parser.add_argument("--save", default="")
+    parser.add_argument("--resume", default="")
     args = parser.parse_args()
-    main(args.max_epochs, args.batch_size, args.backend, args.model, args.save)
+    main(args.max_epochs, args.batch_size, args.backend, args.model, args.save, args.resume)

@@ -392,3 +392,20 @@ def test_graphed_wrappers_refuse_cpu_devices():
         b2.GraphedDataParallel(m, ["cpu", "cpu"], torch.nn.functional.mse_loss, x, y)
     with pytest.raises(ValueError, match="CUDA"):
         b2.GraphedPipeline([m], ["cpu"], 2, torch.nn.functional.mse_loss, x, y)
+
+
+def test_example_saves_and_resumes_under_the_launcher(tmp_path):
+    """examples/ddp_run.py on 2 gloo ranks: one epoch + checkpoint, then --resume continues at epoch 1."""
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    ck = str(tmp_path / "ck.pt")
+    base = [sys.executable, "-m", "pytorch_distributed_training_tutorials_b200.run", "--standalone", "--nproc-per-node", "2",
+            os.path.join(ROOT, "examples", "ddp_run.py"), "--backend", "gloo", "--batch_size", "64"]
+    r = subprocess.run(base + ["--max_epochs", "1", "--save", ck], env=env, capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stderr
+    assert "Epoch: 0, Batch size: 64 | Steps 16]" in r.stdout and os.path.exists(ck)
+    sd = torch.load(ck, map_location="cpu")
+    assert sd["epoch"] == 0 and set(sd["model"].keys()) == {"weight", "bias"}
+    r = subprocess.run(base + ["--max_epochs", "3", "--resume", ck], env=env, capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stderr
+    assert "continuing with epoch 1" in r.stdout
+    assert "Epoch: 0," not in r.stdout and "Epoch: 1," in r.stdout and "Epoch: 2," in r.stdout
