@@ -161,7 +161,6 @@ def timed_e2e_run(run_batches, host_x, host_y, steps: int, warmup: int, world: i
 
 # --------------------------------------------------------------------------- arms
 def run_ours(args, rank, world, local):
-    import pytorch_distributed_training_tutorials_b200 as b2
     from pytorch_distributed_training_tutorials_b200 import _lib, group
     from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
     from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD

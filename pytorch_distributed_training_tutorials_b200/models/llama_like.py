@@ -8,8 +8,6 @@ bitsandbytes); sizes are configurable so tests stay small.
 """
 from __future__ import annotations
 
-import math
-
 import torch
 import torch.nn.functional as F
 from torch import nn

@@ -9,9 +9,8 @@ reference, stages are not registered twice, so ``state_dict()`` has exactly torc
 from __future__ import annotations
 
 import torch
-from torch import nn
 
-from ..parallel.model_parallel import Pipeline, hop
+from ..parallel.model_parallel import hop
 from .resnet import ResNet
 
 

@@ -8,7 +8,6 @@ single ``b200dt_coll_launch`` consumes.
 """
 from __future__ import annotations
 
-import ctypes as C
 from typing import List, Optional, Sequence
 
 import torch

@@ -10,7 +10,6 @@ from typing import Optional, Tuple
 
 import torch
 
-from .. import _lib
 from .._lib import check, lib, on_device, ptr, stream_ptr
 
 BF16 = torch.bfloat16

@@ -15,7 +15,7 @@ machines without GPUs) the same code paths degenerate to plain tensor copies.
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Optional, Sequence
 
 import torch
 

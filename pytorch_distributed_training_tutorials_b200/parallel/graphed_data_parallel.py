@@ -18,7 +18,7 @@ holds the model, the other devices only ever see copies, gradients arrive summed
 from __future__ import annotations
 
 import copy
-from typing import Callable, List, Optional, Sequence
+from typing import Callable, List, Sequence
 
 import torch
 from torch import nn

@@ -10,7 +10,7 @@ pipelined variant is not in the reference; it is required by BASELINE.json (conf
 """
 from __future__ import annotations
 
-from typing import Callable, List, Optional, Sequence
+from typing import List, Optional, Sequence
 
 import torch
 from torch import nn

@@ -8,7 +8,7 @@ execution order; ``dispatch`` moves the blocks and installs hooks that move acti
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Sequence, Tuple, Union
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 from torch import nn

@@ -12,7 +12,7 @@ lock-step).  Not capturable: ``FusedAdam`` (host-side step count), data-dependen
 """
 from __future__ import annotations
 
-from typing import Callable, Optional
+from typing import Callable
 
 import torch
 
