@@ -18,6 +18,7 @@ import torch
 from torch.utils.data import DataLoader
 
 import pytorch_distributed_training_tutorials_b200 as b2
+from pytorch_distributed_training_tutorials_b200.models.toy import ToyLinear
 from pytorch_distributed_training_tutorials_b200.trainer import Trainer
 
 
@@ -33,7 +34,7 @@ def main(max_epochs: int, batch_size: int, backend, model_name: str, save: str, 
         optimizer = b2.FusedSGD(model.parameters(), lr=1e-3)
     else:
         train_dataset = b2.MyTrainDataset(2048)
-        model = torch.nn.Linear(20, 1)
+        model = ToyLinear()
         loss_fn = None                                   # F.cross_entropy, like the reference
         optimizer = torch.optim.SGD(model.parameters(), lr=1e-2)
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, pin_memory=st.device.type == "cuda",

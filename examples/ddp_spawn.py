@@ -16,6 +16,7 @@ import torch
 from torch.utils.data import DataLoader
 
 import pytorch_distributed_training_tutorials_b200 as b2
+from pytorch_distributed_training_tutorials_b200.models.toy import ToyLinear
 from pytorch_distributed_training_tutorials_b200.trainer import Trainer
 
 
@@ -28,7 +29,7 @@ def main(rank: int, world_size: int, max_epochs: int, batch_size: int, backend: 
     train_dataset = b2.MyTrainDataset(2048)
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, pin_memory=torch.cuda.is_available(),
                                   shuffle=False, sampler=b2.DistributedSampler(train_dataset))
-    model = torch.nn.Linear(20, 1)
+    model = ToyLinear()
     optimizer = torch.optim.SGD(model.parameters(), lr=1e-2)
     trainer = Trainer(model=model, gpu_id=rank, optimizer=optimizer, train_dataloader=train_dataloader)
     trainer.train(max_epochs)

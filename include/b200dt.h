@@ -66,6 +66,18 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
  * apply kernels read) followed by one ticket word: 2*C*B200DT_BN_REPLICAS + 1 floats. */
 #define B200DT_BN_REPLICAS 16
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
+/* fp32 SIMT Linear for feature counts the tensor-core path cannot take (K or N not a multiple of 8;
+ * the tutorial's Linear(20,1), (32,2), (10000,10), (10,5)). y[B,N] = x[B,K] * w[N,K]^T + bias (bias may be
+ * NULL); bwd writes any of dx[B,K], dw[N,K], db[N] that is not NULL. The *_host variants run the same
+ * element code serially on the CPU (host pointers): they exist so the indexing is testable without a GPU. */
+int b200dt_skinny_linear_fwd(const float* x, const float* w, const float* bias, float* y, int B, int K,
+                             int N, void* stream);
+int b200dt_skinny_linear_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw,
+                             float* db, int B, int K, int N, void* stream);
+int b200dt_skinny_linear_fwd_host(const float* x, const float* w, const float* bias, float* y, int B,
+                                  int K, int N);
+int b200dt_skinny_linear_bwd_host(const float* dy, const float* x, const float* w, float* dx, float* dw,
+                                  float* db, int B, int K, int N);
 /* Backward of y = relu(linear): g = dy * (y > 0) (bf16, y == g == NULL skips the mask) and
  * db[C] = column sums of g in fp32 (db == NULL skips them); one pass over [rows, C], C % 8 == 0. */
 int b200dt_relu_bwd_bias(const void* dy, const void* y, void* g, float* db, long long rows, int C,

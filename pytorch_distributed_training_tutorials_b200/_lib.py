@@ -55,6 +55,10 @@ _SIGS = {
     "b200dt_bn_stats": [vp, vp, i64, i32, vp],
     "b200dt_bn_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp, vp, vp],
     "b200dt_relu_bwd_bias": [vp, vp, vp, vp, i64, i32, vp],
+    "b200dt_skinny_linear_fwd": [vp, vp, vp, vp, i32, i32, i32, vp],
+    "b200dt_skinny_linear_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "b200dt_skinny_linear_fwd_host": [vp, vp, vp, vp, i32, i32, i32],
+    "b200dt_skinny_linear_bwd_host": [vp, vp, vp, vp, vp, vp, i32, i32, i32],
     "b200dt_bn_apply_eval": [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp],
     "b200dt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
     "b200dt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp],
@@ -123,7 +127,8 @@ def lib() -> "_Counted":
         handle.b200dt_version.restype = C.c_char_p
         handle.b200dt_error_string.restype = C.c_char_p
         handle.b200dt_error_string.argtypes = [i32]
-        _lib = _Counted(handle, [n for n in _SIGS if n not in ("b200dt_enable_peer_access", "b200dt_memcpy_h2d_async")])
+        _lib = _Counted(handle, [n for n in _SIGS if n not in ("b200dt_enable_peer_access", "b200dt_memcpy_h2d_async")
+                                 and not n.endswith("_host")])
         return _lib
 
 

@@ -15,7 +15,10 @@ from ..ops import nn as bnn
 from ..parallel.model_parallel import hop
 
 
-class ToyLinear(nn.Linear):
+class ToyLinear(bnn.Linear):
+    """On a GPU this is the fp32 SIMT kernel of csrc/skinny.cu (20 features: no TMA row pitch), on the
+    CPU plain ``F.linear``; parameters, initialisation and ``state_dict`` keys are nn.Linear's."""
+
     def __init__(self) -> None:
         super().__init__(20, 1)
 
@@ -23,7 +26,7 @@ class ToyLinear(nn.Linear):
 class SampleModel(nn.Module):
     def __init__(self, input_size: int = 32, output_size: int = 2, verbose: bool = True) -> None:
         super().__init__()
-        self.fc = nn.Linear(input_size, output_size)
+        self.fc = bnn.Linear(input_size, output_size)
         self.verbose = verbose
 
     def forward(self, input):
@@ -37,9 +40,9 @@ class ToyModel(nn.Module):
     def __init__(self, dev0="cuda:0", dev1="cuda:1", in_features: int = 10000) -> None:
         super().__init__()
         self.dev0, self.dev1 = torch.device(dev0), torch.device(dev1)
-        self.net1 = nn.Linear(in_features, 10).to(self.dev0)
+        self.net1 = bnn.Linear(in_features, 10).to(self.dev0)
         self.relu = nn.ReLU()
-        self.net2 = nn.Linear(10, 5).to(self.dev1)
+        self.net2 = bnn.Linear(10, 5).to(self.dev1)
 
     def forward(self, x):
         x = self.relu(self.net1(x.to(self.dev0)))

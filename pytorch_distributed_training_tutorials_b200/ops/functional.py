@@ -93,6 +93,36 @@ class _Linear(torch.autograd.Function):
         return dx, dw, db, None, None
 
 
+class _SkinnyLinear(torch.autograd.Function):
+    """fp32 Linear for feature counts the tensor-core path cannot take (the tutorial's Linear(20,1),
+    (32,2), (10000,10), (10,5); ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        x2 = x.reshape(-1, x.shape[-1]).float().contiguous()
+        w = weight.detach().float().contiguous()
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias = bias is not None
+        ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
+        y = NV.skinny_linear_fwd(x2, w, bias.detach().float().contiguous() if bias is not None else None)
+        return y.view(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, weight.shape[0]).float().contiguous()
+        dx, dw, db = NV.skinny_linear_bwd(dy2, x2, weight.detach().float().contiguous(), ctx.needs_input_grad[0],
+                                          ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2])
+        if dx is not None:
+            dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
+        return dx, dw, db
+
+
+def skinny_linear(x, weight, bias=None):
+    """fp32 ``x @ weight^T + bias`` for any (in_features, out_features) on the SIMT kernel."""
+    return _SkinnyLinear.apply(x, weight, bias)
+
+
 def linear(x, weight, bias=None, relu: bool = False, out_fp32: bool = False):
     """y = x @ weight^T + bias on tcgen05; needs in_features % 8 == 0 (TMA row pitch)."""
     return _Linear.apply(x, weight, bias, relu, out_fp32)

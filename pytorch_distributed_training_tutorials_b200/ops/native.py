@@ -96,6 +96,36 @@ def relu_bwd_bias(dy: torch.Tensor, y: Optional[torch.Tensor], want_bias_grad: b
     return g, db
 
 
+def skinny_linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """fp32 ``x[B,K] @ w[N,K]^T + bias`` on the SIMT kernel (any K, N; csrc/skinny.cu)."""
+    _need(x, F32, "x"); _need(w, F32, "w")
+    if bias is not None:
+        _need(bias, F32, "bias")
+    B, K = x.shape
+    N = w.shape[0]
+    y = torch.empty((B, N), device=x.device, dtype=F32)
+    with on_device(x.device):
+        check(lib().b200dt_skinny_linear_fwd(ptr(x), ptr(w), ptr(bias), ptr(y), B, K, N, stream_ptr(x.device)),
+              "skinny_linear_fwd")
+    return y
+
+
+def skinny_linear_bwd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, want_dx: bool, want_dw: bool,
+                      want_db: bool):
+    """Returns ``(dx, dw, db)`` (None where not wanted), all fp32."""
+    _need(dy, F32, "dy"); _need(x, F32, "x"); _need(w, F32, "w")
+    B, K = x.shape
+    N = w.shape[0]
+    dev = x.device
+    dx = torch.empty((B, K), device=dev, dtype=F32) if want_dx else None
+    dw = torch.empty((N, K), device=dev, dtype=F32) if want_dw else None
+    db = torch.empty((N,), device=dev, dtype=F32) if want_db else None
+    with on_device(dev):
+        check(lib().b200dt_skinny_linear_bwd(ptr(dy), ptr(x), ptr(w), ptr(dx), ptr(dw), ptr(db), B, K, N,
+                                             stream_ptr(dev)), "skinny_linear_bwd")
+    return dx, dw, db
+
+
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int = 1, relu: bool = False,
                  bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
     _need(x, BF16, "x"); _need(w, BF16, "w")

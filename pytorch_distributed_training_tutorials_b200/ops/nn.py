@@ -37,9 +37,18 @@ class Linear(nn.Module):
         if not x.is_cuda:
             y = torch.nn.functional.linear(x, self.weight, self.bias)
             return torch.relu(y) if self.relu else y
-        if self.in_features % 8:
-            raise ValueError("b200 Linear needs in_features % 8 == 0 (pad the input features)")
+        if self.skinny:
+            # feature counts the TMA / tcgen05 path cannot take: fp32 SIMT kernel, no library GEMM
+            y = Fn.skinny_linear(x, self.weight, self.bias)
+            return torch.relu(y) if self.relu else y
         return Fn.linear(x, self.weight, self.bias, self.relu, self.out_fp32)
+
+    @property
+    def skinny(self) -> bool:
+        """True for the degenerate layers (K or N not a multiple of 8 and small): the tutorial's
+        Linear(20,1), (32,2), (10000,10), (10,5)."""
+        return self.in_features % 8 != 0 or (self.out_features % 8 != 0
+                                             and self.in_features * self.out_features <= (1 << 20))
 
     def extra_repr(self) -> str:
         return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}"

@@ -409,3 +409,33 @@ def test_example_saves_and_resumes_under_the_launcher(tmp_path):
     assert r.returncode == 0, r.stderr
     assert "continuing with epoch 1" in r.stdout
     assert "Epoch: 0," not in r.stdout and "Epoch: 1," in r.stdout and "Epoch: 2," in r.stdout
+
+
+# --------------------------------------------------------------------------- skinny Linear: host emulation
+@pytest.mark.parametrize("B,K,N", [(32, 20, 1), (8, 32, 2), (20, 10000, 10), (20, 10, 5), (1, 1, 1), (7, 3, 9),
+                                   (300, 17, 33), (2048, 20, 1)])
+def test_skinny_linear_element_code_matches_torch_on_the_host(B, K, N):
+    """csrc/skinny.cu compiles its per-element functions for host and device; the *_host entry points run
+    them serially, so forward / dgrad / wgrad / bias-grad indexing is checked here without a GPU."""
+    from pytorch_distributed_training_tutorials_b200 import _lib
+    L = _lib.lib()
+    torch.manual_seed(B * 7 + K)
+    x = torch.randn(B, K); w = torch.randn(N, K) / K ** 0.5; b = torch.randn(N); dy = torch.randn(B, N)
+    y = torch.full((B, N), float("nan"))
+    assert L.b200dt_skinny_linear_fwd_host(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), B, K, N) == 0
+    ref = torch.nn.functional.linear(x, w, b)
+    assert torch.allclose(y, ref, rtol=1e-4, atol=1e-4), (y - ref).abs().max()
+    y2 = torch.full((B, N), float("nan"))
+    assert L.b200dt_skinny_linear_fwd_host(x.data_ptr(), w.data_ptr(), None, y2.data_ptr(), B, K, N) == 0
+    assert torch.allclose(y2, torch.nn.functional.linear(x, w), rtol=1e-4, atol=1e-4)
+    dx = torch.full((B, K), float("nan")); dw = torch.full((N, K), float("nan")); db = torch.full((N,), float("nan"))
+    assert L.b200dt_skinny_linear_bwd_host(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                                           db.data_ptr(), B, K, N) == 0
+    assert torch.allclose(dx, dy @ w, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(dw, dy.t() @ x, rtol=1e-4, atol=1e-3)
+    assert torch.allclose(db, dy.sum(0), rtol=1e-4, atol=1e-3)
+    # any subset of the three gradients
+    dw2 = torch.full((N, K), float("nan"))
+    assert L.b200dt_skinny_linear_bwd_host(dy.data_ptr(), x.data_ptr(), w.data_ptr(), None, dw2.data_ptr(), None, B, K, N) == 0
+    assert torch.equal(dw2, dw)
+    assert L.b200dt_skinny_linear_fwd_host(x.data_ptr(), w.data_ptr(), None, y.data_ptr(), -1, K, N) == -3
