@@ -19,7 +19,9 @@ for line in txt.splitlines():
 keep = {"tc_gemm_kernel": "tc_gemm_kernel", "coll_kernelILi1ELi8": "coll_twoshot_world8", "coll_kernelILi2": "coll_nvls",
         "coll_kernelILi0": "coll_oneshot", "coll_kernelILi3": "coll_broadcast", "bn_bwd_reduce_kernelILi2": "bn_bwd_reduce_remask",
         "bn_apply_kernelILb1": "bn_apply_train", "multi_opt_kernelILb0": "multi_sgd", "p2p_bcast_kernel": "p2p_broadcast",
-        "p2p_reduce_kernel": "p2p_reduce", "mse_static_kernelIf": "mse_static"}
+        "p2p_reduce_kernel": "p2p_reduce", "mse_static_kernelIf": "mse_static",
+        "skinny_fwd_kernel": "skinny_linear_fwd", "relu_bwd_bias_kernel": "relu_bwd_bias",
+        "stem_im2col_kernel": "stem_im2col", "maxpool_bwd_kernel": "maxpool_bwd"}
 pats = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "SYNCS", "LDGMC", "STGMC", "ATOMG", "REDG", "HMMA", "ELECT", "UBLKCP"]
 rows = []
 for name, body in funcs.items():
