@@ -35,12 +35,23 @@ def parse_args(argv: Optional[List[str]] = None) -> argparse.Namespace:
     p.add_argument("--local-addr", "--local_addr", dest="local_addr", type=str, default=None)
     p.add_argument("--max-restarts", "--max_restarts", dest="max_restarts", type=int, default=0)
     p.add_argument("--monitor-interval", "--monitor_interval", dest="monitor_interval", type=float, default=0.1)
-    p.add_argument("--run-id", "--rdzv-id", dest="run_id", type=str, default=None)
+    p.add_argument("--run-id", "--rdzv-id", "--rdzv_id", dest="run_id", type=str, default=None)
+    p.add_argument("--rdzv-endpoint", "--rdzv_endpoint", dest="rdzv_endpoint", type=str, default=None,
+                   help="host[:port] of rank 0, torchrun spelling of --master-addr / --master-port")
+    p.add_argument("--rdzv-backend", "--rdzv_backend", dest="rdzv_backend", type=str, default="static",
+                   help="accepted for torchrun command lines; the rendezvous is always the static TCP store")
     p.add_argument("-m", "--module", action="store_true", help="treat the script as a python module name")
     p.add_argument("--no-python", "--no_python", dest="no_python", action="store_true")
     p.add_argument("training_script", type=str)
     p.add_argument("training_script_args", nargs=argparse.REMAINDER)
-    return p.parse_args(argv)
+    args = p.parse_args(argv)
+    if args.rdzv_endpoint:
+        host, _, port = args.rdzv_endpoint.partition(":")
+        if host:
+            args.master_addr = host
+        if port:
+            args.master_port = int(port)
+    return args
 
 
 def resolve_nproc(spec: str) -> int:

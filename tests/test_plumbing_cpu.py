@@ -439,3 +439,13 @@ def test_skinny_linear_element_code_matches_torch_on_the_host(B, K, N):
     assert L.b200dt_skinny_linear_bwd_host(dy.data_ptr(), x.data_ptr(), w.data_ptr(), None, dw2.data_ptr(), None, B, K, N) == 0
     assert torch.equal(dw2, dw)
     assert L.b200dt_skinny_linear_fwd_host(x.data_ptr(), w.data_ptr(), None, y.data_ptr(), -1, K, N) == -3
+
+
+def test_launcher_accepts_torchrun_rendezvous_spelling():
+    from pytorch_distributed_training_tutorials_b200.run import parse_args
+    a = parse_args(["--nproc_per_node", "2", "--rdzv-backend", "c10d", "--rdzv-endpoint", "10.0.0.5:29611",
+                    "--rdzv-id", "job7", "train.py", "--max_epochs", "3"])
+    assert (a.master_addr, a.master_port, a.run_id, a.nproc_per_node) == ("10.0.0.5", 29611, "job7", "2")
+    assert a.training_script == "train.py" and a.training_script_args == ["--max_epochs", "3"]
+    b = parse_args(["--rdzv_endpoint", "localhost", "train.py"])
+    assert (b.master_addr, b.master_port) == ("localhost", 29500)
