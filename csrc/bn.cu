@@ -15,7 +15,8 @@ namespace b200 {
 constexpr int kBnThreads = 256;
 constexpr int kUnroll = 4;
 constexpr int kUnrollBwd = 4;
-constexpr int kRep = B200DT_BN_REPLICAS;   // copies of the partial-sum array: spreads the atomics of ~900 CTAs       // independent 16-byte loads in flight per thread and stream
+// The partial-sum array behind `sums` has b200::bn_replicas() copies: 16 normally (spreads the atomics
+// of ~900 CTAs), one per row-slab CTA in deterministic mode (plain stores, folded in slab order).
 
 struct Slab {
   int cols_per_block;   // vector (8-channel) columns handled by one CTA
@@ -34,6 +35,7 @@ static Slab make_slab(long long rows, int C, int target_blocks) {
   long long gy = target_blocks / gx;
   const long long max_gy = (rows + s.rows_per_iter - 1) / s.rows_per_iter;
   if (gy > max_gy) gy = max_gy;
+  if (deterministic() && gy > bn_replicas()) gy = bn_replicas();     // one partial-sum copy per row slab
   if (gy < 1) gy = 1;
   s.grid = dim3(gx, (unsigned)gy, 1);
   return s;
@@ -45,7 +47,7 @@ static Slab make_slab(long long rows, int C, int target_blocks) {
 // all threads (no serial tail on a few threads).
 template <int NACC>
 __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int cols, int C,
-                                             float* smem, float* __restrict__ out) {
+                                             float* smem, float* __restrict__ out, int reps, int det) {
   constexpr int NV = NACC * 8;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nwarps = kBnThreads / 32;
@@ -69,14 +71,15 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
     if (col >= cv) continue;
     float s = 0.f;
     for (int w = 0; w < nwarps; ++w) s += smem[(w * NV + v) * cols + x];
-    atomicAdd(out + (size_t)(blockIdx.y % kRep) * 2 * C + (v >> 3) * C + col * 8 + (v & 7), s);
+    if (det) out[(size_t)blockIdx.y * 2 * C + (v >> 3) * C + col * 8 + (v & 7)] = s;   // slab-owned copy
+    else atomicAdd(out + (size_t)(blockIdx.y % reps) * 2 * C + (v >> 3) * C + col * 8 + (v & 7), s);
   }
   // The last CTA to finish folds the replicas into copy 0, so consumers read one plain array.
   __shared__ bool is_last;
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    unsigned int* ticket = reinterpret_cast<unsigned int*>(out + (size_t)kRep * 2 * C);
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(out + (size_t)reps * 2 * C);
     is_last = (atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1);
   }
   __syncthreads();
@@ -84,8 +87,9 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
     __threadfence();
     for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) {
       float t = 0.f;
-#pragma unroll
-      for (int r = 0; r < kRep; ++r) t += *reinterpret_cast<volatile float*>(out + (size_t)r * 2 * C + i);
+      const int nrep = det ? (int)gridDim.y : reps;
+#pragma unroll 4
+      for (int r = 0; r < nrep; ++r) t += *reinterpret_cast<volatile float*>(out + (size_t)r * 2 * C + i);
       out[i] = t;
     }
   }
@@ -93,7 +97,7 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
 
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long rows, int C,
-                int cols, int rowlanes) {
+                int cols, int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
@@ -123,14 +127,7 @@ bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long
       for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] += f[j] * f[j]; }
     }
   }
-  fold_and_add<2>(acc, tx, cols, C, smem, sums);
-}
-
-__device__ __forceinline__ float rep_sum(const float* __restrict__ sums, int C, int idx) {
-  float s = 0.f;
-#pragma unroll
-  for (int r = 0; r < kRep; ++r) s += sums[(size_t)r * 2 * C + idx];
-  return s;
+  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, det);
 }
 
 template <bool kTrain>
@@ -225,7 +222,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                      const float* __restrict__ save_invstd, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ sums,
                      uint4* __restrict__ dres, long long rows, int C, int relu, int cols,
-                     int rowlanes) {
+                     int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
@@ -286,7 +283,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
       }
     }
   }
-  fold_and_add<2>(acc, tx, cols, C, smem, sums);
+  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, det);
 }
 
 template <int kMask>
@@ -366,12 +363,14 @@ using namespace b200;
 extern "C" int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * (2 * C * kRep + 1), st);
+  const int reps = bn_replicas();
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * ((size_t)2 * C * reps + 1), st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
   bn_stats_kernel<<<s.grid, kBnThreads, smem, st>>>(reinterpret_cast<const uint4*>(x), sums, rows, C,
-                                                    s.cols_per_block, s.rows_per_iter);
+                                                    s.cols_per_block, s.rows_per_iter, reps,
+                                                    deterministic());
   return (int)cudaGetLastError();
 }
 
@@ -411,7 +410,8 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
   if (relu && y == nullptr && (gamma == nullptr || beta == nullptr)) return -3;
   if (relu == 2 && (y == nullptr || dres == nullptr)) return -3;   // bit-mask mode materialises the masked gradient
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * (2 * C * kRep + 1), st);
+  const int reps = bn_replicas();
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * ((size_t)2 * C * reps + 1), st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
@@ -420,7 +420,8 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
   bn_bwd_reduce_kernel<M><<<s.grid, kBnThreads, smem, st>>>(                                       \
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
       reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
-      reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter)
+      reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter, reps,      \
+      deterministic())
   if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1);
   else if (mask == 2) B200_LAUNCH_REDUCE(2); else B200_LAUNCH_REDUCE(3);
 #undef B200_LAUNCH_REDUCE

@@ -53,4 +53,12 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 
 inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
+// Library-wide switches (csrc/config.cu).  deterministic(): every floating-point sum that is normally
+// combined with atomics (BatchNorm statistics, split-K weight gradients, bias gradients) is combined in
+// a fixed order instead, so the same launch on the same inputs gives the same bits.
+int deterministic();
+// Copies of the partial-sum array behind a BatchNorm `sums` buffer: B200DT_BN_REPLICAS normally, one
+// per possible CTA slot (B200DT_BN_REPLICAS_DET) in deterministic mode.
+int bn_replicas();
+
 }  // namespace b200

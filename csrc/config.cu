@@ -1,0 +1,29 @@
+// Library-wide switches.  The only one so far is the deterministic-reduction mode: a debugging /
+// regression-testing aid with no counterpart call in the reference (which inherits
+// torch.use_deterministic_algorithms from its substrate and never sets it).
+#include <atomic>
+#include <stdlib.h>
+#include "common.cuh"
+#include "../include/b200dt.h"
+
+namespace b200 {
+
+static std::atomic<int> g_det{-1};
+
+int deterministic() {
+  int v = g_det.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200DT_DETERMINISTIC");
+    v = (e != nullptr && e[0] != '\0' && e[0] != '0') ? 1 : 0;
+    g_det.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
+int bn_replicas() { return deterministic() ? B200DT_BN_REPLICAS_DET : B200DT_BN_REPLICAS; }
+
+}  // namespace b200
+
+extern "C" void b200dt_set_deterministic(int on) { b200::g_det.store(on ? 1 : 0, std::memory_order_relaxed); }
+extern "C" int b200dt_get_deterministic(void) { return b200::deterministic(); }
+extern "C" int b200dt_bn_replicas(void) { return b200::bn_replicas(); }

@@ -60,6 +60,10 @@ struct GemmParams {
   int b_mn;                 // kind 0 only: B operand is MN-major (dgrad reads the filter un-transposed)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   const float* bias;
+  // deterministic mode (b200::deterministic()): sums are combined in a fixed order
+  int det;                  // 1: no floating-point atomics anywhere in this launch
+  int bn_reps;              // copies of {sum, sumsq}[bn_C] behind bn_sums (ticket word follows them)
+  long long split_stride;   // WGRAD, det: split s writes its partial tile to C + s * split_stride
 };
 
 struct TmaMaps {
@@ -309,6 +313,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int n_blk = t % p.tiles_n;
       const int m_blk = (t / p.tiles_n) % p.tiles_m;
+      const int split = t / (p.tiles_n * p.tiles_m);
       const int col_base = n_blk * p.BN;   // WGRAD: taps are consecutive, tap * Cin + ct * BN
       int tw = 0, th = 0, tn = 0;
       if (p.kind == 0) {
@@ -326,7 +331,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         if (p.kind == 0) {
           c1 = tw * p.bw + p.qoff[q][0]; c2 = th * p.bh + p.qoff[q][1]; c3 = tn * p.bn + p.qoff[q][2];
         } else {
-          c1 = m_blk * kBM + q * 32; c2 = 0; c3 = 0;
+          c1 = m_blk * kBM + q * 32; c2 = p.split_stride ? split : 0; c3 = 0;
         }
         uint8_t* my_row = buf + lane * 128;
         const int sw = lane & 7;
@@ -427,8 +432,20 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
             }
             float* accb = col_acc;
             const int cc = sl * 64 + lane * 2;
-            atomicAdd(accb + cc, s0); atomicAdd(accb + cc + 1, s1);
-            atomicAdd(accb + 256 + cc, q0); atomicAdd(accb + 256 + cc + 1, q1);
+            if (!p.det) {
+              atomicAdd(accb + cc, s0); atomicAdd(accb + cc + 1, s1);
+              atomicAdd(accb + 256 + cc, q0); atomicAdd(accb + 256 + cc + 1, q1);
+            } else {
+              // fixed order: the four quarter-warps that share this slab (same pi) add in turn
+#pragma unroll 1
+              for (int turn = 0; turn < 4; ++turn) {
+                if (turn == q) {
+                  accb[cc] += s0; accb[cc + 1] += s1;
+                  accb[256 + cc] += q0; accb[256 + cc + 1] += q1;
+                }
+                if (turn < 3) asm volatile("bar.sync %0, 128;" ::"r"(3 + pi) : "memory");
+              }
+            }
           }
           if (lane == 0) {
             if (p.atomic)
@@ -460,7 +477,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         } else {
           const int r = m_blk * kBM + row;
           row_ok = r < p.m_valid;
-          row_off = static_cast<long long>(r) * p.sW;
+          row_off = static_cast<long long>(r) * p.sW + split * p.split_stride;
         }
         for (int c = pi; c < p.BN / 32; c += 2) {
           uint32_t v[32];
@@ -489,13 +506,18 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         // sums to global memory (spread over the replicas) and clear the buffer for tile t + 2
         asm volatile("bar.sync 2, 256;" ::: "memory");
         float* accb = col_acc;
-        float* dstb = p.bn_sums + (size_t)(blockIdx.x % B200DT_BN_REPLICAS) * 2 * p.bn_C;
+        // det: this CTA owns copy blockIdx.x and column c is always handled by the same thread, so a
+        // plain read-modify-write in tile order replaces the atomics
+        float* dstb = p.bn_sums + (size_t)(p.det ? blockIdx.x : blockIdx.x % p.bn_reps) * 2 * p.bn_C;
         const int e = (warp - 2) * 32 + lane;          // 0..255: one column per thread
         if (e < p.BN) {
           const int c = col_base + e;
           const float sv = accb[e], qv = accb[256 + e];
           accb[e] = 0.f; accb[256 + e] = 0.f;
-          if (c < p.n_valid) { atomicAdd(dstb + c, sv); atomicAdd(dstb + p.bn_C + c, qv); }
+          if (c < p.n_valid) {
+            if (p.det) { dstb[c] += sv; dstb[p.bn_C + c] += qv; }
+            else { atomicAdd(dstb + c, sv); atomicAdd(dstb + p.bn_C + c, qv); }
+          }
         }
         asm volatile("bar.sync 2, 256;" ::: "memory");      // cleared before the next tile adds
       }
@@ -508,7 +530,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       asm volatile("bar.sync 2, 256;" ::: "memory");
       uint32_t mine = 0, fold_last = 0;
       if (threadIdx.x == 64) {
-        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.bn_sums + (size_t)B200DT_BN_REPLICAS * 2 * p.bn_C);
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.bn_sums + (size_t)p.bn_reps * 2 * p.bn_C);
         mine = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
       }
       // broadcast the verdict through the barrier's OR-reduction (no static shared memory: the
@@ -521,8 +543,9 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         __threadfence();
         for (int i = threadIdx.x - 64; i < 2 * p.bn_C; i += 256) {
           float tsum = 0.f;
-#pragma unroll
-          for (int r = 0; r < B200DT_BN_REPLICAS; ++r)
+          const int nrep = p.det ? min(p.bn_reps, (int)gridDim.x) : p.bn_reps;
+#pragma unroll 4
+          for (int r = 0; r < nrep; ++r)
             tsum += *reinterpret_cast<volatile float*>(p.bn_sums + (size_t)r * 2 * p.bn_C + i);
           p.bn_sums[i] = tsum;
         }
@@ -639,6 +662,8 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   if (stages < 2) return -2;
   p.stages = stages;
   p.tma_store = mapC != nullptr ? 1 : 0;
+  p.det = deterministic();
+  p.bn_reps = bn_replicas();
 
   const int smem = stages * stage_bytes + fixed;
   // function attributes are per device: opt in to the large dynamic smem once on each
@@ -653,6 +678,7 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   }
   const int total = p.tiles_m * p.tiles_n * p.splits;
   int grid = total < num_sms() ? total : num_sms();
+  if (p.det && p.bn_sums != nullptr && grid > p.bn_reps) grid = p.bn_reps;   // one statistics slot per CTA
   if (grid <= 0) return 0;
   TmaMaps maps;
   for (int i = 0; i < kMaxMaps; ++i) { maps.a[i] = mapsA[i]; maps.b[i] = mapsB[i]; }
@@ -708,6 +734,44 @@ static void pick_box(int W, int H, int target, int* bw, int* bh, int* bn) {
   *bn = target / (best_w * best_h);
 }
 
+// Deterministic split-K: every split writes its partial [M, ld_s] tile set to a scratch slab and this
+// kernel adds the slabs in split order (out = (out +) sum_s part[s]).
+__global__ void splitk_fold_kernel(const float* __restrict__ part, float* __restrict__ out, int M, int N,
+                                   int ld_s, long long ldc, int splits, long long split_stride,
+                                   int accumulate) {
+  const long long total = (long long)M * N;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int m = (int)(i / N), n = (int)(i - (long long)m * N);
+    const float* src = part + (long long)m * ld_s + n;
+    float acc = accumulate ? out[m * ldc + n] : 0.f;
+    for (int sidx = 0; sidx < splits; ++sidx) acc += src[sidx * split_stride];
+    out[m * ldc + n] = acc;
+  }
+}
+
+// Stream-ordered scratch for the deterministic split-K path (allocated and freed on the launch
+// stream, so concurrent streams never share it and a graph capture records both nodes).
+static int det_split_begin(GemmParams& p, int M, int N, cudaStream_t st, float** part, int* ld_s) {
+  *ld_s = (N + 3) & ~3;
+  const size_t bytes = sizeof(float) * (size_t)p.splits * M * (*ld_s);
+  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(part), bytes, st);
+  if (e != cudaSuccess) return (int)e;
+  p.C = *part; p.sW = *ld_s; p.split_stride = (long long)M * (*ld_s); p.atomic = 0;
+  return 0;
+}
+static int det_split_end(const GemmParams& p, float* part, int ld_s, float* out, int M, int N,
+                         long long ldc, int accumulate, cudaStream_t st) {
+  const long long total = (long long)M * N;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  splitk_fold_kernel<<<blocks, 256, 0, st>>>(part, out, M, N, ld_s, ldc, p.splits, p.split_stride,
+                                             accumulate);
+  cudaError_t e = cudaGetLastError();
+  cudaError_t f = cudaFreeAsync(part, st);
+  return (int)(e != cudaSuccess ? e : f);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -715,7 +779,7 @@ using namespace b200;
 // C[M,N] (bf16 or fp32) = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU)     -- all row-major, bf16 inputs.
 static int clear_bn_sums(float* bn_sums, int C, cudaStream_t st) {
   if (bn_sums == nullptr) return 0;
-  return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * B200DT_BN_REPLICAS + 1), st);
+  return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * bn_replicas() + 1), st);
 }
 
 extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K,
@@ -802,7 +866,13 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
   p.taps[0] = Tap{0, 0, 0, 0};
   p.C = C; p.sW = ldc; p.n_valid = N; p.m_valid = M;
   p.out_fp32 = 1; p.relu = 0; p.atomic = p.splits > 1; p.bias = nullptr;
-  if (clear) {
+  const bool det_split = deterministic() && p.splits > 1;
+  float* part = nullptr;
+  int ld_s = 0;
+  if (det_split) {
+    int e = det_split_begin(p, M, N, (cudaStream_t)stream, &part, &ld_s);
+    if (e) return e;
+  } else if (clear) {
     cudaError_t e = cudaMemsetAsync(C, 0, sizeof(float) * (size_t)ldc * M, (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
   }
@@ -819,15 +889,22 @@ extern "C" int b200dt_gemm_nt_reduce_bf16(const void* A, const void* B, float* C
   if (r) return r;
   mb[1] = mb[2] = mb[3] = mb[0];
   CUtensorMap mc;
-  long long dimsC[4] = {N, M, 1, 1};
-  long long strC[3] = {ldc, (long long)ldc * M, (long long)ldc * M};
+  const long long ldo = det_split ? ld_s : ldc;
+  long long dimsC[4] = {N, M, det_split ? p.splits : 1, 1};
+  long long strC[3] = {ldo, ldo * M, ldo * M * (det_split ? p.splits : 1)};
   int boxC[4] = {32, 32, 1, 1};
-  const bool tma_out = out_map_ok(C, strC, true);
+  const bool tma_out = out_map_ok(p.C, strC, true);
   if (tma_out) {
-    r = make_map_out(&mc, C, dimsC, strC, boxC, true);
+    r = make_map_out(&mc, p.C, dimsC, strC, boxC, true);
     if (r) return r;
   }
-  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
+  r = launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
+  if (det_split) {
+    // caller-chosen splits accumulate into C (documented contract); library-chosen ones overwrite
+    const int r2 = det_split_end(p, part, ld_s, C, M, N, ldc, clear ? 0 : 1, (cudaStream_t)stream);
+    if (r == 0) r = r2;
+  }
+  return r;
 }
 
 // NHWC conv2d forward as implicit GEMM.  x: [NB, H, W, Cin] bf16, w: [Cout, R, S, Cin] bf16,
@@ -941,7 +1018,13 @@ extern "C" int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw
   p.W = Wo; p.H = Ho; p.NB = NB;
   p.C = dw; p.sW = (long long)p.ntaps * Cin; p.n_valid = p.ntaps * Cin; p.m_valid = Cout;
   p.out_fp32 = 1; p.relu = 0; p.atomic = p.splits > 1; p.bias = nullptr;
-  if (p.atomic) {
+  const bool det_split = deterministic() && p.splits > 1;
+  float* part = nullptr;
+  int ld_s = 0;
+  if (det_split) {
+    int e = det_split_begin(p, Cout, n_total, (cudaStream_t)stream, &part, &ld_s);
+    if (e) return e;
+  } else if (p.atomic) {
     cudaError_t e = cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)Cout * p.ntaps * Cin,
                                     (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
@@ -981,15 +1064,20 @@ extern "C" int b200dt_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw
       }
   }
   CUtensorMap mc;
-  long long dimsC[4] = {(long long)p.ntaps * Cin, Cout, 1, 1};
-  long long strC[3] = {p.sW, p.sW * Cout, p.sW * Cout};
+  long long dimsC[4] = {(long long)p.ntaps * Cin, Cout, det_split ? p.splits : 1, 1};
+  long long strC[3] = {p.sW, p.sW * Cout, p.sW * Cout * (det_split ? p.splits : 1)};
   int boxC[4] = {32, 32, 1, 1};
-  const bool tma_out = out_map_ok(dw, strC, true);
+  const bool tma_out = out_map_ok(p.C, strC, true);
   if (tma_out) {
-    r = make_map_out(&mc, dw, dimsC, strC, boxC, true);
+    r = make_map_out(&mc, p.C, dimsC, strC, boxC, true);
     if (r) return r;
   }
-  return launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
+  r = launch(ma, mb, tma_out ? &mc : nullptr, p, (cudaStream_t)stream);
+  if (det_split) {
+    const int r2 = det_split_end(p, part, ld_s, dw, Cout, n_total, n_total, 0, (cudaStream_t)stream);
+    if (r == 0) r = r2;
+  }
+  return r;
 }
 
 // Zero one phase view of a NHWC tensor (used when no filter tap reaches that phase).

@@ -90,7 +90,7 @@ extern "C" int b200dt_relu_bwd_bias(const void* dy, const void* y, void* g, floa
   long long gy = (148LL * 8 + gx - 1) / gx;
   const long long max_gy = (rows + (long long)lanes * kPwUnroll - 1) / ((long long)lanes * kPwUnroll);
   if (gy > max_gy) gy = max_gy;
-  if (gy < 1) gy = 1;
+  if (gy < 1 || (db != nullptr && deterministic())) gy = 1;   // det: one CTA per column group, one add per column
   relu_bwd_bias_kernel<<<dim3(gx, (unsigned)gy), kPwThreads, 0, st>>>(
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
       reinterpret_cast<uint4*>(g), db, rows, C, cols, lanes);

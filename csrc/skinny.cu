@@ -13,6 +13,7 @@
 #include "../include/b200dt.h"
 
 namespace b200 {
+int deterministic();        // csrc/config.cu
 
 #define B200_HD __host__ __device__ __forceinline__
 
@@ -103,6 +104,7 @@ __global__ void skinny_bgrad_kernel(const float* dy, float* db, int B, int N, in
 
 // Number of reduction slices: enough threads to fill the machine for long reductions, one for short.
 static int pick_slices(long long outputs, int reduce_len) {
+  if (deterministic()) return 1;     // one thread per output: no atomics to order
   int s = 1;
   while (s < 256 && (long long)s * outputs < 148LL * 256 && s * 8 < reduce_len) s *= 2;
   return s;

@@ -65,6 +65,16 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
  * spread their atomics over the copies and the last CTA folds them into copy 0, which is what the
  * apply kernels read) followed by one ticket word: 2*C*B200DT_BN_REPLICAS + 1 floats. */
 #define B200DT_BN_REPLICAS 16
+/* Deterministic mode (env B200DT_DETERMINISTIC=1 or b200dt_set_deterministic(1); no counterpart call in
+ * the reference, it is a regression-testing aid): every fp32 sum that is otherwise combined with atomics
+ * (BatchNorm statistics, BatchNorm-backward partials, split-K weight gradients, bias gradients, the SIMT
+ * Linear's slices) is combined in a fixed order, so identical launches give identical bits. `sums` buffers
+ * then hold B200DT_BN_REPLICAS_DET copies (one per CTA slot): size them with b200dt_bn_replicas(). Split-K
+ * weight gradients take a stream-ordered scratch (cudaMallocAsync / cudaFreeAsync on the launch stream). */
+#define B200DT_BN_REPLICAS_DET 160
+void b200dt_set_deterministic(int on);
+int b200dt_get_deterministic(void);
+int b200dt_bn_replicas(void);
 int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream);
 /* fp32 SIMT Linear for feature counts the tensor-core path cannot take (K or N not a multiple of 8;
  * the tutorial's Linear(20,1), (32,2), (10000,10), (10,5)). y[B,N] = x[B,K] * w[N,K]^T + bias (bias may be

@@ -124,12 +124,29 @@ def lib() -> "_Counted":
         handle.b200dt_coll_chunk_bytes.restype = i32
         handle.b200dt_coll_chunk_bytes.argtypes = []
         handle.b200dt_device_sm_count.restype = i32
+        handle.b200dt_set_deterministic.restype = None
+        handle.b200dt_set_deterministic.argtypes = [i32]
+        handle.b200dt_get_deterministic.restype = i32
+        handle.b200dt_get_deterministic.argtypes = []
+        handle.b200dt_bn_replicas.restype = i32
+        handle.b200dt_bn_replicas.argtypes = []
         handle.b200dt_version.restype = C.c_char_p
         handle.b200dt_error_string.restype = C.c_char_p
         handle.b200dt_error_string.argtypes = [i32]
         _lib = _Counted(handle, [n for n in _SIGS if n not in ("b200dt_enable_peer_access", "b200dt_memcpy_h2d_async")
                                  and not n.endswith("_host")])
         return _lib
+
+
+def set_deterministic(on: bool = True) -> None:
+    """Fixed-order reductions in every kernel of the library (BatchNorm statistics, split-K weight gradients,
+    bias gradients): the same step on the same inputs gives the same bits.  Also settable with
+    ``B200DT_DETERMINISTIC=1`` in the environment.  Slower; meant for regression tests and debugging."""
+    lib().b200dt_set_deterministic(int(bool(on)))
+
+
+def is_deterministic() -> bool:
+    return bool(lib().b200dt_get_deterministic())
 
 
 def check(rc: int, what: str = "") -> None:

@@ -14,7 +14,11 @@ from .._lib import check, lib, on_device, ptr, stream_ptr
 
 BF16 = torch.bfloat16
 F32 = torch.float32
-BN_REPLICAS = 16          # B200DT_BN_REPLICAS in include/b200dt.h
+
+
+def bn_replicas() -> int:
+    """Copies of the partial-sum array behind a BatchNorm ``sums`` buffer (16; 160 in deterministic mode)."""
+    return int(lib().b200dt_bn_replicas())
 
 
 def _need(t: torch.Tensor, dtype, name: str) -> None:
@@ -26,7 +30,7 @@ def _need(t: torch.Tensor, dtype, name: str) -> None:
 # --------------------------------------------------------------------------- GEMM / conv
 def bn_sums_buffer(C: int, device) -> torch.Tensor:
     """Scratch for BatchNorm statistics: replicated {sum, sum of squares} + ticket (see bn.cu)."""
-    return torch.empty(2 * C * BN_REPLICAS + 1, device=device, dtype=F32)
+    return torch.empty(2 * C * bn_replicas() + 1, device=device, dtype=F32)
 
 
 def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
@@ -226,7 +230,7 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------- batch norm
 def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
     rows, Cc = x2d.shape
-    sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=x2d.device, dtype=F32)
+    sums = torch.empty(2 * Cc * bn_replicas() + 1, device=x2d.device, dtype=F32)
     with on_device(x2d.device):
         check(lib().b200dt_bn_stats(ptr(x2d), ptr(sums), rows, Cc, stream_ptr(x2d.device)), "bn_stats")
     return sums
@@ -275,7 +279,7 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
     if relu and relu_mask is not None:
         dres = torch.empty_like(dy2d)
         dx = torch.empty_like(x2d)
-        sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=dev, dtype=F32)
+        sums = torch.empty(2 * Cc * bn_replicas() + 1, device=dev, dtype=F32)
         dgamma = torch.empty(Cc, device=dev, dtype=F32)
         dbeta = torch.empty(Cc, device=dev, dtype=F32)
         with on_device(dev):
@@ -287,7 +291,7 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
                                             ptr(gamma), ptr(beta), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta),
                                             rows, Cc, 0, st), "bn_bwd_apply")
         return dx, dgamma, dbeta, (dres if want_dres else None)
-    sums = torch.empty(2 * Cc * BN_REPLICAS + 1, device=dev, dtype=F32)
+    sums = torch.empty(2 * Cc * bn_replicas() + 1, device=dev, dtype=F32)
     dres = torch.empty_like(dy2d) if want_dres else None
     dx = torch.empty_like(x2d)
     dgamma = torch.empty(Cc, device=dev, dtype=F32)
