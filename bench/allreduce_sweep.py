@@ -35,7 +35,7 @@ def main():
     st = group.init(backend="nccl")
     dev, world, rank = st.device, st.world_size, st.rank
     max_bytes = args.max_mb << 20
-    arena = coll.SymmetricArena(max_bytes + (1 << 20), dev)
+    arena = coll.make_arena(max_bytes + (1 << 20), dev)
     modes = ["oneshot", "twoshot"] + (["nvls"] if arena.has_multicast else [])
     rows = []
     size = 1024

@@ -8,7 +8,7 @@ from pytorch_distributed_training_tutorials_b200.ops import collectives as coll
 from pytorch_distributed_training_tutorials_b200.utils.timing import time_cuda
 st = group.init(backend="nccl", rank=0, world_size=1)
 dev = st.device
-arena = coll.SymmetricArena((1 << 30) + (1 << 20), dev)
+arena = coll.make_arena((1 << 30) + (1 << 20), dev)
 plain = torch.empty((1 << 30) + (1 << 20), dtype=torch.uint8, device=dev)
 for mb in (64, 1024):
     n = (mb << 20) // 4

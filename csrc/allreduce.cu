@@ -17,8 +17,14 @@
 //
 // CTA b of every rank owns the same chunks in every phase, so only CTA-local flags are needed and
 // the kernel never requires all CTAs to be co-resident.  Flags are consumed (1 -> 0) by the waiter,
-// so a slot can be reused by the next barrier without epochs.  Spins are bounded: on timeout the
-// kernel records it in *status and falls through, and the host raises.
+// so a slot can be reused by the next barrier without epochs.  Waits are bounded in TIME
+// (%globaltimer): a rank that waits longer than the limit writes {code, CTA, peer} into the status
+// words (pinned host memory, readable by the host at any moment), raises the abort word in every peer's
+// signal pad so that they stop waiting too, and TRAPS: the averaged gradients are never written from
+// partial data, the process dies loudly on its next CUDA call and the launcher tears the job down --
+// what ProcessGroupNCCL's watchdog does for the reference's all-reduce (ddp_gpus.py:38).
+#include <atomic>
+#include <stdlib.h>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "../include/b200dt.h"
@@ -52,12 +58,34 @@ struct CollArgs {
   int wire_bf16;            // dtype on the wire / in staging
   float scale;
   int sig_base;             // first signal word this launch may use
-  int* status;
-  unsigned long long spin_limit;
+  int* status;              // {code, cta << 8 | peer, elapsed ms}; host-mapped when the arena provides it
+  unsigned long long timeout_ns;
   int in_place;             // tensors live (or are copied unscaled) in the staging region; the result stays there
 };
 
 constexpr int kCollThreads = 512;
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// A wait exceeded the limit (code 1: a peer never consumed my previous flag; 2: a peer's flag never
+// arrived) or a peer raised the abort word (code 3).  Never returns.
+__device__ __noinline__ void barrier_abort(const CollArgs& a, int code, int peer, unsigned long long waited_ns) {
+  if (a.status != nullptr) {
+    // plain stores (the words may live in host memory; whichever waiter gets here last wins)
+    volatile int* st = a.status;
+    st[1] = (int)((blockIdx.x << 8) | (unsigned)peer);
+    st[2] = (int)(waited_ns / 1000000ull);
+    __threadfence_system();
+    st[0] = code;
+  }
+  for (int r = 0; r < a.world; ++r) st_relaxed_sys(a.sigs[r] + B200DT_SIGNAL_WORDS - 1, 1u);
+  __threadfence_system();
+  __trap();
+}
 
 __device__ __forceinline__ void block_barrier(const CollArgs& a) {
   __syncthreads();
@@ -65,14 +93,26 @@ __device__ __forceinline__ void block_barrier(const CollArgs& a) {
   if (t < a.world) {
     const int slot = a.sig_base + blockIdx.x * a.world;
     uint32_t* remote = a.sigs[t] + slot + a.rank;
-    unsigned long long spins = 0;
+    const uint32_t* abort_word = a.sigs[a.rank] + B200DT_SIGNAL_WORDS - 1;
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
     while (cas_release_sys(remote, 0u, 1u) != 0u) {
-      if (++spins > a.spin_limit) { atomicExch(a.status, 1); break; }
+      if ((++spins & 255u) == 0) {
+        const unsigned long long now = global_ns();
+        if (t0 == 0) t0 = now;
+        if (ld_relaxed_sys(abort_word) != 0u) barrier_abort(a, 3, t, now - t0);
+        if (now - t0 > a.timeout_ns) barrier_abort(a, 1, t, now - t0);
+      }
     }
     uint32_t* local = a.sigs[a.rank] + slot + t;
-    spins = 0;
+    spins = 0; t0 = 0;
     while (cas_acquire_sys(local, 1u, 0u) != 1u) {
-      if (++spins > a.spin_limit) { atomicExch(a.status, 2); break; }
+      if ((++spins & 255u) == 0) {
+        const unsigned long long now = global_ns();
+        if (t0 == 0) t0 = now;
+        if (ld_relaxed_sys(abort_word) != 0u) barrier_abort(a, 3, t, now - t0);
+        if (now - t0 > a.timeout_ns) barrier_abort(a, 2, t, now - t0);
+      }
     }
   }
   __syncthreads();
@@ -475,9 +515,27 @@ __global__ void cast_to_f32_kernel(const void* __restrict__ src, float* __restri
                       : reinterpret_cast<const float*>(src)[i];
 }
 
+// Wait limit of the flag barriers: B200DT_COLL_TIMEOUT_S (seconds, fractional allowed), default 30 s.
+static std::atomic<long long> g_timeout_ns{-1};
+static unsigned long long coll_timeout_ns() {
+  long long v = g_timeout_ns.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200DT_COLL_TIMEOUT_S");
+    double sec = e != nullptr ? atof(e) : 30.0;
+    if (!(sec > 0.0)) sec = 30.0;
+    v = (long long)(sec * 1e9);
+    g_timeout_ns.store(v, std::memory_order_relaxed);
+  }
+  return (unsigned long long)v;
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" void b200dt_set_coll_timeout_ms(long long ms) {
+  g_timeout_ns.store(ms > 0 ? ms * 1000000ll : -1, std::memory_order_relaxed);
+}
 
 extern "C" int b200dt_coll_chunk_bytes(void) { return (int)sizeof(CollChunk); }
 
@@ -490,13 +548,14 @@ extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t
                                   const void* chunks, int n_chunks, long long stage_base_bytes,
                                   int tensor_bf16, int wire_bf16, float scale, int sig_base,
                                   int grid, int* status, int in_place, void* stream) {
-  if (world < 1 || world > B200DT_MAX_WORLD || n_chunks <= 0) return world < 1 ? -3 : 0;
+  if (world < 1 || world > B200DT_MAX_WORLD) return -3;
+  if (n_chunks <= 0) return 0;
   if (mode == kNvls && mc == 0) return -4;
   // in place: every rank overwrites the slice it owns, which only two-shot / NVLS make race-free,
   // and the tensors must already have the wire dtype
   if (in_place && (mode == kOneShot || mode == kBcast || (wire_bf16 != 0) != (tensor_bf16 != 0))) return -3;
   if (grid < 1) grid = 1;
-  if (sig_base + grid * world > B200DT_SIGNAL_WORDS) return -5;
+  if (sig_base < 0 || sig_base + grid * world > B200DT_SIGNAL_WORDS - 1) return -5;   // last word = abort flag
   CollArgs a{};
   for (int r = 0; r < world; ++r) {
     a.bufs[r] = reinterpret_cast<void*>(bufs[r]);
@@ -510,7 +569,7 @@ extern "C" int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t
   a.stage_base = stage_base_bytes;
   a.tensor_bf16 = tensor_bf16; a.wire_bf16 = wire_bf16 || tensor_bf16;
   a.scale = scale; a.sig_base = sig_base; a.status = status;
-  a.spin_limit = 1ull << 26;     // ~ tens of seconds of polling before giving up
+  a.timeout_ns = coll_timeout_ns();
   a.in_place = in_place;
   cudaStream_t st = (cudaStream_t)stream;
   switch (mode) {

@@ -5,14 +5,23 @@
 // (bucket i is never launched before bucket i-1, so every rank issues the cross-GPU kernels in
 // the same order and the flag protocol cannot deadlock), the record of the order in which
 // gradients became ready (used to rebuild the buckets after the first iteration) and the
-// end-of-backward callback.  What a "launch" is (the fused sm_100a all-reduce on a side stream,
-// or a gloo / NCCL all-reduce on CPU) is decided by the Python wrapper through two callbacks.
+// end-of-backward callback.  On GPUs the reducer also LAUNCHES: given a native plan (one descriptor per
+// bucket, set_native_plan) it records the ready event, makes the side stream wait for it, refreshes the
+// bucket's device-side pointer table from pinned staging when a gradient moved, and calls
+// b200dt_coll_launch -- all from the autograd thread, without the GIL and without touching Python.  The
+// finalize callback joins the side stream, re-points .grad at the arena views and reads the collectives'
+// host-mapped status word, raising when a peer timed out.  Without a plan (CPU / gloo, the NCCL opt-out,
+// debug handshake, tracing) "launch" and "finalize" are two Python callbacks.
 //
 // Counterpart in the reference's stack: c10d::Reducer, reached from
 // /root/reference/ddp_gpus.py:32,38 (spec: torch/csrc/distributed/c10d/reducer.hpp).
 #include <torch/extension.h>
 #include <torch/csrc/autograd/engine.h>
 #include <torch/csrc/autograd/utils/lambda_post_hook.h>
+#include <c10/cuda/CUDACachingAllocator.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <cuda_runtime.h>
 
 #include <atomic>
 #include <chrono>
@@ -85,6 +94,49 @@ std::pair<std::vector<std::vector<int64_t>>, std::vector<int64_t>> assign_bucket
   return {out, out_caps};
 }
 
+
+// ---- native launch plan ---------------------------------------------------------------------
+// Signature of b200dt_coll_launch (include/b200dt.h); the address comes from the ctypes handle.
+typedef int (*CollLaunchFn)(int, const uint64_t*, const uint64_t*, uint64_t, int, int, int, const void*,
+                            const void*, int, long long, int, int, float, int, int, int*, int, void*);
+
+#define B200_CUDA_OK(expr)                                                                         \
+  do {                                                                                             \
+    cudaError_t e__ = (expr);                                                                      \
+    TORCH_CHECK(e__ == cudaSuccess, #expr, " failed: ", cudaGetErrorString(e__));                  \
+  } while (0)
+
+struct PinnedSlot {
+  int64_t* host = nullptr;
+  cudaEvent_t done = nullptr;
+  bool used = false;
+};
+
+struct NativeBucket {
+  int mode = 0, n_chunks = 0, tensor_bf16 = 0, wire_bf16 = 0, sig_base = 0, grid = 1, in_place = 0;
+  long long stage_base = 0;
+  float scale = 1.f;
+  uint64_t tensors_dev = 0, chunks_dev = 0;
+  int64_t nbytes = 0;
+  std::vector<int64_t> param_ids, numels;
+  std::vector<at::Tensor> views;          // gradient views living in the arena (may be empty)
+  std::vector<uint64_t> last_ptrs;
+  std::vector<PinnedSlot> ring;
+  size_t ring_pos = 0;
+};
+
+struct NativePlan {
+  bool enabled = false;
+  CollLaunchFn fn = nullptr;
+  uint64_t bufs[8] = {0}, sigs[8] = {0};
+  uint64_t mc = 0, status_dev = 0;
+  volatile int* status_host = nullptr;
+  int rank = 0, world = 1, device = 0;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ready_ev = nullptr, done_ev = nullptr;
+  std::vector<NativeBucket> buckets;
+};
+
 class Reducer {
  public:
   Reducer(std::vector<at::Tensor> params, std::vector<std::vector<int64_t>> buckets,
@@ -115,7 +167,83 @@ class Reducer {
     }
   }
 
-  ~Reducer() { remove_hooks(); }
+  ~Reducer() {
+    remove_hooks();
+    clear_native_plan();
+  }
+
+  // plan: {"launch_fn": addr, "bufs": [...], "sigs": [...], "mc": int, "status_dev": int, "status_host": addr,
+  //        "rank", "world", "device", "side_stream": cudaStream_t as int,
+  //        "buckets": [{"mode","n_chunks","tensor_bf16","wire_bf16","sig_base","grid","in_place","stage_base",
+  //                     "scale","tensors_dev","chunks_dev","nbytes","param_ids","numels","views"}]}
+  void set_native_plan(const py::dict& plan) {
+    clear_native_plan();
+    NativePlan np;
+    np.fn = reinterpret_cast<CollLaunchFn>(plan["launch_fn"].cast<uintptr_t>());
+    auto bufs = plan["bufs"].cast<std::vector<uint64_t>>();
+    auto sigs = plan["sigs"].cast<std::vector<uint64_t>>();
+    np.world = plan["world"].cast<int>();
+    TORCH_CHECK(np.world >= 1 && np.world <= 8 && bufs.size() == (size_t)np.world && sigs.size() == (size_t)np.world,
+                "native plan: bad world / pointer tables");
+    for (int r = 0; r < np.world; ++r) { np.bufs[r] = bufs[r]; np.sigs[r] = sigs[r]; }
+    np.mc = plan["mc"].cast<uint64_t>();
+    np.status_dev = plan["status_dev"].cast<uint64_t>();
+    np.status_host = reinterpret_cast<volatile int*>(plan["status_host"].cast<uintptr_t>());
+    np.rank = plan["rank"].cast<int>();
+    np.device = plan["device"].cast<int>();
+    np.side = reinterpret_cast<cudaStream_t>(plan["side_stream"].cast<uintptr_t>());
+    c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(np.device));
+    B200_CUDA_OK(cudaEventCreateWithFlags(&np.ready_ev, cudaEventDisableTiming));
+    B200_CUDA_OK(cudaEventCreateWithFlags(&np.done_ev, cudaEventDisableTiming));
+    for (auto item : plan["buckets"].cast<py::list>()) {
+      py::dict d = item.cast<py::dict>();
+      NativeBucket b;
+      b.mode = d["mode"].cast<int>();
+      b.n_chunks = d["n_chunks"].cast<int>();
+      b.tensor_bf16 = d["tensor_bf16"].cast<int>();
+      b.wire_bf16 = d["wire_bf16"].cast<int>();
+      b.sig_base = d["sig_base"].cast<int>();
+      b.grid = d["grid"].cast<int>();
+      b.in_place = d["in_place"].cast<int>();
+      b.stage_base = d["stage_base"].cast<long long>();
+      b.scale = d["scale"].cast<float>();
+      b.tensors_dev = d["tensors_dev"].cast<uint64_t>();
+      b.chunks_dev = d["chunks_dev"].cast<uint64_t>();
+      b.nbytes = d["nbytes"].cast<int64_t>();
+      b.param_ids = d["param_ids"].cast<std::vector<int64_t>>();
+      b.numels = d["numels"].cast<std::vector<int64_t>>();
+      if (d.contains("views") && !d["views"].is_none()) b.views = d["views"].cast<std::vector<at::Tensor>>();
+      TORCH_CHECK(b.numels.size() == b.param_ids.size(), "native plan: numels / param_ids mismatch");
+      TORCH_CHECK(b.views.empty() || b.views.size() == b.param_ids.size(), "native plan: views / param_ids mismatch");
+      b.ring.resize(4);
+      for (auto& sl : b.ring) {
+        B200_CUDA_OK(cudaHostAlloc(reinterpret_cast<void**>(&sl.host), sizeof(int64_t) * 2 * b.param_ids.size() + 16,
+                                   cudaHostAllocDefault));
+        B200_CUDA_OK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+      }
+      np.buckets.push_back(std::move(b));
+    }
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      TORCH_CHECK(np.buckets.size() == buckets_.size(), "native plan must describe every bucket");
+      np.enabled = true;
+      native_ = std::move(np);
+    }
+  }
+
+  void clear_native_plan() {
+    std::lock_guard<std::mutex> lock(mu_);
+    if (!native_.enabled && native_.buckets.empty()) return;
+    for (auto& b : native_.buckets)
+      for (auto& sl : b.ring) {
+        if (sl.done) { cudaEventSynchronize(sl.done); cudaEventDestroy(sl.done); }
+        if (sl.host) cudaFreeHost(sl.host);
+      }
+    if (native_.ready_ev) cudaEventDestroy(native_.ready_ev);
+    if (native_.done_ev) cudaEventDestroy(native_.done_ev);
+    native_ = NativePlan{};
+  }
+  bool has_native_plan() const { return native_.enabled; }
 
   void remove_hooks() {
     for (auto& h : hooks_) h.second->del_post_hook(h.first);
@@ -137,6 +265,7 @@ class Reducer {
     TORCH_CHECK(covered == params_.size(), "buckets must cover every parameter exactly once");
     pending_.assign(buckets_.size(), 0);
     expecting_ = false;
+    native_.enabled = false;        // a new layout needs a new plan (set_native_plan)
   }
 
   // Called by the wrapper after forward when this backward must synchronise gradients.
@@ -171,6 +300,10 @@ class Reducer {
     d["last_first_launch_us"] = t_first_launch_ ? t_first_launch_ - t_prepare_ : 0;
     d["last_last_launch_us"] = t_last_launch_ ? t_last_launch_ - t_prepare_ : 0;
     d["last_finalize_us"] = t_finalize_ ? t_finalize_ - t_prepare_ : 0;
+    d["native_launches"] = native_launches_;
+    d["native_bytes"] = native_bytes_;
+    d["native_table_uploads"] = native_uploads_;
+    d["native_plan"] = native_.enabled;
     return d;
   }
 
@@ -209,6 +342,16 @@ class Reducer {
       torch::autograd::Engine::get_default_engine().queue_callback([this] { this->finalize(); });
     }
     if (!to_launch.empty()) {
+      if (native_.enabled) {
+        for (int64_t b : to_launch) {
+          const int64_t t = now_us();
+          if (t_first_launch_ == 0) t_first_launch_ = t;
+          t_last_launch_ = t;
+          launch_native(static_cast<size_t>(b));
+          ++launched_;
+        }
+        return;
+      }
       py::gil_scoped_acquire gil;
       for (int64_t b : to_launch) {
         const int64_t t = now_us();
@@ -217,6 +360,104 @@ class Reducer {
         on_bucket_ready_(b);
         ++launched_;
       }
+    }
+  }
+
+  // One bucket: ready event -> side stream -> (pointer table refresh) -> fused collective.  No GIL.
+  void launch_native(size_t bi) {
+    NativePlan& np = native_;
+    NativeBucket& b = np.buckets[bi];
+    if (np.world == 1) return;
+    c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(np.device));
+    cudaStream_t cur = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(np.device)).stream();
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    B200_CUDA_OK(cudaStreamIsCapturing(cur, &cap));
+    const bool capturing = cap == cudaStreamCaptureStatusActive;
+    B200_CUDA_OK(cudaEventRecord(np.ready_ev, cur));
+    B200_CUDA_OK(cudaStreamWaitEvent(np.side, np.ready_ev, 0));
+    const size_t n = b.param_ids.size();
+    bool changed = b.last_ptrs.size() != n;
+    if (changed) b.last_ptrs.assign(n, 0);
+    auto side_stream = c10::cuda::getStreamFromExternal(np.side, static_cast<c10::DeviceIndex>(np.device));
+    for (size_t k = 0; k < n; ++k) {
+      const at::Tensor& g = params_[b.param_ids[k]].grad();
+      TORCH_CHECK(g.defined(), "parameter ", b.param_ids[k], " has no gradient at bucket launch");
+      TORCH_CHECK(g.is_contiguous(), "parameter ", b.param_ids[k], " has a non-contiguous .grad; the fused "
+                  "all-reduce reads gradients in place (make the gradient contiguous or use allreduce='nccl')");
+      TORCH_CHECK(g.numel() == b.numels[k], "gradient of parameter ", b.param_ids[k], " changed its size");
+      const uint64_t ptr = reinterpret_cast<uint64_t>(g.data_ptr());
+      if (ptr != b.last_ptrs[k]) { b.last_ptrs[k] = ptr; changed = true; }
+      if (!capturing) c10::cuda::CUDACachingAllocator::recordStream(g.storage().data_ptr(), side_stream);
+    }
+    if (changed) upload_table(np, b, capturing);
+    const int rc = np.fn(b.mode, np.bufs, np.sigs, (b.mode == 2 || b.mode == 3) ? np.mc : 0, np.rank, np.world, 0,
+                         reinterpret_cast<const void*>(b.tensors_dev), reinterpret_cast<const void*>(b.chunks_dev),
+                         b.n_chunks, b.stage_base, b.tensor_bf16, b.wire_bf16, b.scale, b.sig_base, b.grid,
+                         reinterpret_cast<int*>(np.status_dev), b.in_place, np.side);
+    TORCH_CHECK(rc == 0, "b200dt_coll_launch failed for bucket ", bi, ": rc ", rc,
+                rc > 0 ? cudaGetErrorString(static_cast<cudaError_t>(rc)) : "");
+    ++native_launches_;
+    native_bytes_ += b.nbytes;
+  }
+
+  void upload_table(NativePlan& np, NativeBucket& b, bool capturing) {
+    const size_t n = b.param_ids.size();
+    const size_t bytes = sizeof(int64_t) * 2 * n;
+    PinnedSlot* slot = nullptr;
+    PinnedSlot frozen;
+    if (capturing) {
+      // the captured memcpy node re-reads its source on every replay: give it a buffer of its own that is
+      // never written again (relaxed capture mode: cudaHostAlloc is not a stream operation)
+      cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+      B200_CUDA_OK(cudaThreadExchangeStreamCaptureMode(&mode));
+      cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&frozen.host), bytes + 16, cudaHostAllocDefault);
+      cudaThreadExchangeStreamCaptureMode(&mode);
+      B200_CUDA_OK(e);
+      slot = &frozen;
+    } else {
+      for (size_t tries = 0; tries < b.ring.size(); ++tries) {
+        PinnedSlot& c = b.ring[(b.ring_pos + tries) % b.ring.size()];
+        if (!c.used || cudaEventQuery(c.done) == cudaSuccess) { slot = &c; b.ring_pos = (b.ring_pos + tries + 1) % b.ring.size(); break; }
+      }
+      if (slot == nullptr) {
+        slot = &b.ring[b.ring_pos];
+        b.ring_pos = (b.ring_pos + 1) % b.ring.size();
+        B200_CUDA_OK(cudaEventSynchronize(slot->done));
+      }
+    }
+    for (size_t k = 0; k < n; ++k) {
+      slot->host[2 * k] = static_cast<int64_t>(b.last_ptrs[k]);
+      slot->host[2 * k + 1] = b.numels[k];
+    }
+    B200_CUDA_OK(cudaMemcpyAsync(reinterpret_cast<void*>(b.tensors_dev), slot->host, bytes, cudaMemcpyHostToDevice, np.side));
+    if (!capturing) {
+      B200_CUDA_OK(cudaEventRecord(slot->done, np.side));
+      slot->used = true;
+    }
+    ++native_uploads_;
+  }
+
+  void finalize_native() {
+    NativePlan& np = native_;
+    if (np.world == 1) return;
+    c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(np.device));
+    cudaStream_t cur = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(np.device)).stream();
+    B200_CUDA_OK(cudaEventRecord(np.done_ev, np.side));
+    B200_CUDA_OK(cudaStreamWaitEvent(cur, np.done_ev, 0));
+    for (auto& b : np.buckets) {
+      for (size_t k = 0; k < b.views.size(); ++k) {
+        at::Tensor& p = params_[b.param_ids[k]];
+        const at::Tensor& g = p.grad();
+        // the reduced gradients are in the arena: point .grad at them (no copy back)
+        if (!g.defined() || g.data_ptr() != b.views[k].data_ptr()) p.mutable_grad() = b.views[k];
+      }
+    }
+    if (np.status_host != nullptr && np.status_host[0] != 0) {
+      const int code = np.status_host[0], where = np.status_host[1], ms = np.status_host[2];
+      TORCH_CHECK(false, "rank ", np.rank, ": peer-memory collective gave up after ", ms, " ms waiting for rank ",
+                  where & 0xFF, " (CTA ", where >> 8, ", status ", code,
+                  "): a rank died, hung, or issued its collectives in another order. The kernel trapped instead of "
+                  "reducing partial data.");
     }
   }
 
@@ -232,6 +473,10 @@ class Reducer {
       finalized_ = true;
       ++iterations_;
       t_finalize_ = now_us();
+    }
+    if (native_.enabled) {
+      finalize_native();
+      return;
     }
     py::gil_scoped_acquire gil;
     on_finalize_();
@@ -251,6 +496,8 @@ class Reducer {
   int64_t iterations_ = 0;
   std::atomic<int64_t> hooks_fired_{0};
   int64_t t_prepare_ = 0, t_first_launch_ = 0, t_last_launch_ = 0, t_finalize_ = 0;
+  NativePlan native_;
+  int64_t native_launches_ = 0, native_bytes_ = 0, native_uploads_ = 0;
 };
 
 }  // namespace
@@ -273,5 +520,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("finalized", &Reducer::finalized)
       .def("remove_hooks", &Reducer::remove_hooks)
       .def("install_hooks", &Reducer::install_hooks)
+      .def("set_native_plan", &Reducer::set_native_plan)
+      .def("clear_native_plan", &Reducer::clear_native_plan)
+      .def("has_native_plan", &Reducer::has_native_plan)
       .def("stats", &Reducer::stats);
 }

@@ -190,8 +190,12 @@ int b200dt_multi_adam(const long long* meta, const int* chunks, int n_chunks, fl
  * B200DT_SIGNAL_WORDS of them). `mc` is the multicast address of the symmetric buffer (0 if none;
  * required for mode 2). `tensors`: device array of {void* ptr; int64 numel}. `chunks`: device array
  * of {int32 tensor, int32 start, int32 len, int32 pad, int64 stage_off}; stage_off is in elements,
- * a multiple of 8. All ranks must pass identical chunk tables, `grid` and `sig_base`. `status`
- * (device int32) becomes non-zero if a peer did not arrive within the spin bound.
+ * a multiple of 8. All ranks must pass identical chunk tables, `grid` and `sig_base`; launches that may
+ * run concurrently (different streams) need disjoint [sig_base, sig_base + grid*world) ranges, and the
+ * last signal word is reserved (abort flag). `status` (3 x int32, ideally host-mapped memory from
+ * b200dt_status_alloc) receives {code, cta << 8 | peer, waited ms} when a flag wait exceeds the time limit
+ * (B200DT_COLL_TIMEOUT_S, default 30 s; b200dt_set_coll_timeout_ms); the kernel then raises the abort
+ * word in every peer's pad and traps, so no rank ever writes gradients reduced from partial data.
  * in_place != 0 (modes 1 and 2, wire dtype == tensor dtype): the staging region is the home of the
  * tensors ("gradients as bucket views"): a tensor whose address already is its staging slot is not
  * copied, others are copied in unscaled, `scale` is applied to the SUM, and nothing is copied back
@@ -199,6 +203,7 @@ int b200dt_multi_adam(const long long* meta, const int* chunks, int n_chunks, fl
 #define B200DT_SIGNAL_WORDS 8192
 #define B200DT_MAX_WORLD 8
 int b200dt_coll_chunk_bytes(void);
+void b200dt_set_coll_timeout_ms(long long ms);
 int b200dt_coll_launch(int mode, const uint64_t* bufs, const uint64_t* sigs, uint64_t mc, int rank,
                        int world, int root, const void* tensors, const void* chunks, int n_chunks,
                        long long stage_base_bytes, int tensor_bf16, int wire_bf16, float scale,
@@ -212,6 +217,30 @@ int b200dt_cast_to_f32(const void* src, float* dst, long long n, int src_bf16, v
  * dtype 0 fp32, 1 bf16 (for tests on one GPU). bufs: HOST array of device addresses. */
 int b200dt_allreduce_local_emulate(const uint64_t* bufs, int world, void* out, long long n,
                                    int dtype, float scale, void* stream);
+
+/* ---------------------------------------------------------------- symmetric arena (csrc/arena.cu)
+ * Replaces the buffer registration / peer mapping ProcessGroupNCCL does behind init_process_group
+ * (ddp_gpus.py:16): one cuMemCreate allocation per rank, exported as a POSIX fd, mapped into every peer
+ * process, and bound to ONE NVLS multicast object (cuMulticastCreate / AddDevice / BindMem) whose address
+ * the multimem kernels use. fds travel between processes out of band (ops/arena.py uses AF_UNIX sockets).
+ * Call order: create (all) -> export_fd / map_peer (all pairs) -> mc_create (rank 0) / mc_import (others)
+ * -> mc_add_device (all) -> barrier -> mc_bind (all) -> barrier. Returns -7 when a driver call fails
+ * (b200dt_arena_last_error gives the CUresult). */
+int b200dt_multicast_supported(int dev);
+int b200dt_arena_create(int dev, int rank, int world, long long nbytes, void** arena, long long* size_out);
+int b200dt_arena_export_fd(void* arena, int* fd);
+int b200dt_arena_map_peer(void* arena, int peer, int fd);
+int b200dt_arena_mc_create(void* arena, int* fd);
+int b200dt_arena_mc_import(void* arena, int fd);
+int b200dt_arena_mc_add_device(void* arena);
+int b200dt_arena_mc_bind(void* arena);
+unsigned long long b200dt_arena_ptr(void* arena, int peer);
+unsigned long long b200dt_arena_mc_ptr(void* arena);
+int b200dt_arena_last_error(void* arena);
+int b200dt_arena_destroy(void* arena);
+/* 64 bytes of pinned host memory mapped into the device: the collectives' status words. */
+int b200dt_status_alloc(int** host_ptr, unsigned long long* dev_ptr);
+int b200dt_status_free(int* host_ptr);
 
 /* ---------------------------------------------------------------- single-process peer kernels
  * Replaces torch._C._broadcast_coalesced / _scatter / _gather / nccl.reduce behind nn.DataParallel

@@ -165,6 +165,8 @@ def check(rc: int, what: str = "") -> None:
         -4: "NVLS requested but no multicast address",
         -5: "not enough signal-pad words for this grid",
         -6: "peer access not possible between these devices",
+        -7: "a CUDA driver call failed (b200dt_arena_last_error has the CUresult)",
+        -9: "input larger than the fixed scratch of this entry point",
     }
     raise RuntimeError(f"b200dt {what}: error {rc}: {reasons.get(rc, 'tensor map encode failed' if rc < -1000 else 'invalid argument')}")
 

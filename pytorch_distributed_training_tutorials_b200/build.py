@@ -122,6 +122,7 @@ def build_reducer(force: bool = False, verbose: bool = False) -> Path:
         sources=[str(s) for s in srcs],
         extra_include_paths=[str(ROOT / "include")],
         extra_cflags=["-O2", "-std=c++17"],
+        with_cuda=True,                     # CUDA runtime headers + libcudart / c10_cuda (the reducer launches kernels)
         build_directory=str(build_dir),
         verbose=verbose,
         is_python_module=True,

@@ -1,13 +1,17 @@
 """Symmetric-memory arena and launch helpers for the fused cross-GPU collectives.
 
-The arena is one peer-mapped staging buffer plus one signal pad per rank, obtained from
-``torch.distributed._symmetric_memory`` (cuMem + fabric handles + NVLS multicast binding are
-plumbing; the kernels that use the pointers are ours, ``csrc/allreduce.cu``).  ``TensorTable``
-turns a list of tensors (one DDP bucket) into the device-side pointer / chunk tables that a
-single ``b200dt_coll_launch`` consumes.
+The arena is one peer-mapped staging buffer plus one signal pad per rank.  Two flavours with the same
+surface: ``arena.DriverArena`` (the library's own cuMem / cuMulticast bring-up, ``csrc/arena.cu``; the
+default, and the one that gives the NVLS kernels their multicast address) and ``SymmetricArena`` on top of
+``torch.distributed._symmetric_memory`` (fallback; ``B200DT_ARENA=torch`` selects it).  The kernels that use
+the pointers are ours either way (``csrc/allreduce.cu``).  ``TensorTable`` turns a list of tensors (one DDP
+bucket) into the device-side pointer / chunk tables that a single ``b200dt_coll_launch`` consumes.
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
+import sys
 from typing import List, Optional, Sequence
 
 import torch
@@ -22,8 +26,102 @@ CHUNK_ELEMS = 16384
 ONESHOT_MAX_BYTES = 256 * 1024
 
 
+class CollectiveTimeout(RuntimeError):
+    """A peer-memory collective waited longer than B200DT_COLL_TIMEOUT_S for a peer."""
+
+
+class StatusWords:
+    """The collectives' status words: 64 bytes of pinned host memory mapped into the device.  The kernels
+    write ``{code, cta << 8 | peer, waited ms}`` there before they trap; the host reads them without
+    touching any stream (so it works after the CUDA context has been poisoned by the trap)."""
+
+    _CODES = {1: "a peer never consumed this rank's previous flag (it is stuck or dead)",
+              2: "a peer's flag never arrived (it died, hung, or issued its collectives in another order)",
+              3: "a peer timed out first and raised the abort flag"}
+
+    def __init__(self) -> None:
+        h = lib()._handle
+        h.b200dt_status_alloc.argtypes = [C.POINTER(C.POINTER(C.c_int)), C.POINTER(C.c_ulonglong)]
+        h.b200dt_status_free.argtypes = [C.POINTER(C.c_int)]
+        self._host = C.POINTER(C.c_int)()
+        dev = C.c_ulonglong()
+        check(h.b200dt_status_alloc(C.byref(self._host), C.byref(dev)), "status_alloc")
+        self.dev_ptr = int(dev.value)
+
+    def code(self) -> int:
+        return int(self._host[0])
+
+    def check(self, rank: int = -1) -> None:
+        c = self.code()
+        if c:
+            where = int(self._host[1])
+            raise CollectiveTimeout(
+                f"rank {rank}: peer-memory collective gave up after {int(self._host[2])} ms waiting for rank "
+                f"{where & 0xFF} (CTA {where >> 8}): {self._CODES.get(c, 'status ' + str(c))}. The kernel trapped "
+                "instead of reducing partial data; this process's CUDA context is no longer usable.")
+
+    def clear(self) -> None:
+        self._host[0] = 0
+
+
+class _SignalRanges:
+    """Hands out disjoint ranges of signal words: every stream-level user of an arena (a DDP instance's
+    bucket stream, its broadcast stream, a free-standing ``all_reduce_``) gets its own, so launches that may
+    overlap on the GPU never share flags.  All ranks must request ranges in the same order."""
+
+    def __init__(self, total: int) -> None:
+        self.total = total - 1        # the last word is the abort flag
+        self.next = 0
+
+    def take(self, words: int) -> int:
+        words = (int(words) + 31) // 32 * 32
+        if self.next + words > self.total:
+            raise RuntimeError(f"out of signal words ({self.next} + {words} > {self.total}); create a second arena")
+        base = self.next
+        self.next += words
+        return base
+
+
+def signal_base(arena, key: str, max_blocks: int = 32) -> int:
+    """The signal-word range of user ``key`` on ``arena`` (allocated on first use, same order on all ranks)."""
+    table = arena.__dict__.setdefault("_sig_users", {})
+    if key not in table:
+        ranges = arena.__dict__.setdefault("_sig_ranges", _SignalRanges(SIGNAL_WORDS))
+        table[key] = ranges.take(max_blocks * arena.world)
+    return table[key]
+
+
+def make_arena(nbytes: int, device: torch.device, group=None, flavour: Optional[str] = None):
+    """``flavour``: "driver" (own cuMem / cuMulticast bring-up), "torch" (torch symmetric memory) or None = env
+    ``B200DT_ARENA`` / driver first, torch as fallback.  All ranks take the same decision."""
+    flavour = flavour or os.environ.get("B200DT_ARENA", "auto")
+    group = group if group is not None else dist.group.WORLD
+    if flavour in ("auto", "driver"):
+        from .arena import DriverArena
+        err = None
+        arena = None
+        try:
+            arena = DriverArena(nbytes, device, group)
+        except Exception as e:  # noqa: BLE001 - any failure means "use the other flavour", decided collectively
+            err = f"{type(e).__name__}: {e}"
+        votes = [None] * dist.get_world_size(group)
+        dist.all_gather_object(votes, err, group=group)
+        bad = [f"rank {r}: {v}" for r, v in enumerate(votes) if v]
+        if not bad:
+            return arena
+        if arena is not None:
+            arena.close()
+        if flavour == "driver":
+            raise RuntimeError("driver-API arena bring-up failed: " + "; ".join(bad))
+        print(f"[b200dt] driver-API arena unavailable ({'; '.join(bad)}); using torch symmetric memory",
+              file=sys.stderr, flush=True)
+    return SymmetricArena(nbytes, device, group)
+
+
 class SymmetricArena:
     """Per-rank symmetric staging buffer + signal pad, mapped into every peer of the group."""
+
+    flavour = "torch"
 
     def __init__(self, nbytes: int, device: torch.device, group=None) -> None:
         import torch.distributed._symmetric_memory as symm_mem
@@ -53,7 +151,8 @@ class SymmetricArena:
         self.multicast_ptr = mc
         self._bufs_c = u64_array(self.buf_ptrs)
         self._sigs_c = u64_array(self.sig_ptrs)
-        self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        self.status_words = StatusWords()
+        self.multicast_error = None if mc else "torch symmetric memory reports no multicast support"
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group, device_ids=[device.index])   # every pad is zero before first use
 
@@ -61,11 +160,12 @@ class SymmetricArena:
     def has_multicast(self) -> bool:
         return self.multicast_ptr != 0
 
+    @property
+    def status(self):
+        return self.status_words
+
     def check_status(self) -> None:
-        s = int(self.status.item())
-        if s:
-            raise RuntimeError(f"peer-memory collective timed out waiting for a peer (status {s}); "
-                               "a rank died or the ranks issued collectives in different orders")
+        self.status_words.check(self.rank)
 
     def close(self) -> None:
         self.hdl = self.sig_hdl = None
@@ -75,7 +175,8 @@ class SymmetricArena:
 def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> str:
     if requested != "auto":
         if requested == "nvls" and not arena.has_multicast:
-            raise RuntimeError("allreduce='nvls' requested but the arena has no multicast mapping")
+            raise RuntimeError("allreduce='nvls' requested but the arena has no multicast mapping "
+                               f"({getattr(arena, 'multicast_error', None)})")
         return requested
     # one-shot pulls (world-1) x the payload into every rank: only worth it for latency-bound
     # messages, and the break-even shrinks with the number of peers (measured: profiles/)
@@ -143,20 +244,28 @@ class TensorTable:
         key = tuple(t.data_ptr() for t in tensors)
         if key == self._ptr_key:
             return
+        want = torch.bfloat16 if self.tensor_bf16 else None
         for i, t in enumerate(tensors):
             assert t.numel() == self.numels[i] and t.is_contiguous()
+            if want is not None and t.dtype != want or (want is None and t.element_size() != 4):
+                raise TypeError(f"tensor {i} of this table is {t.dtype}; the table was built for "
+                                f"{'bf16' if self.tensor_bf16 else '32-bit'} tensors")
             self._host[2 * i] = t.data_ptr()
             self._host[2 * i + 1] = t.numel()
         self._uploader.upload(self.tensors, self._host, stream)
         self._ptr_key = key
 
 
-def launch(mode: str, arena: SymmetricArena, table: TensorTable, scale: float, stream: torch.cuda.Stream,
-           root: int = 0, sig_base: int = 0, max_blocks: int = 32, stage_base: int = 0,
+def launch(mode: str, arena, table: TensorTable, scale: float, stream: torch.cuda.Stream,
+           root: int = 0, sig_base: Optional[int] = None, max_blocks: int = 32, stage_base: int = 0,
            in_place: bool = False) -> None:
     """``stage_base``: byte offset of this table's staging region inside the arena.  ``in_place``: the
-    tensors' home IS that region (see ``stage_views``): no copy-in for resident tensors, no copy-out."""
+    tensors' home IS that region (see ``stage_views``): no copy-in for resident tensors, no copy-out.
+    ``sig_base``: first signal word of the caller's own range (``signal_base``); None = the range of
+    the stream the launch goes to."""
     grid = table.grid(max_blocks)
+    if sig_base is None:
+        sig_base = signal_base(arena, f"stream:{stream.cuda_stream}", max(max_blocks, 32))
     if stage_base + table.stage_bytes > arena.nbytes:
         raise RuntimeError(f"bucket of {table.stage_bytes} bytes at offset {stage_base} does not fit the "
                            f"{arena.nbytes}-byte arena")
@@ -166,7 +275,7 @@ def launch(mode: str, arena: SymmetricArena, table: TensorTable, scale: float, s
         check(lib().b200dt_coll_launch(MODE[mode], arena._bufs_c, arena._sigs_c, arena.multicast_ptr if mode in ("nvls", "bcast") else 0,
                                        arena.rank, arena.world, root, ptr(table.tensors), ptr(table.chunks),
                                        table.n_chunks, int(stage_base), int(table.tensor_bf16), int(table.wire_bf16),
-                                       scale, sig_base, grid, ptr(arena.status), int(in_place),
+                                       scale, sig_base, grid, arena.status_words.dev_ptr, int(in_place),
                                        stream.cuda_stream), f"coll_launch[{mode}]")
 
 

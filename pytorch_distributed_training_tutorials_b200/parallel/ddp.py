@@ -20,6 +20,7 @@ Same construction-time and per-step contract as the wrapper the reference uses a
 from __future__ import annotations
 
 import contextlib
+import ctypes
 import os
 import sys
 import time
@@ -30,7 +31,7 @@ import torch.distributed as dist
 from torch import nn
 
 from .. import group as _group
-from ..utils.timing import trace_range
+from ..utils.timing import TRACE as _TRACE, trace_range
 from ._native_reducer import load as _load_reducer
 
 FIRST_BUCKET_BYTES = 1024 * 1024
@@ -112,13 +113,15 @@ class DistributedDataParallel(nn.Module):
 
         R = _load_reducer()
         self._R = R
-        # iteration 1: one bucket holding every parameter (launch once, learn the ready order)
+        # iteration 1: one bucket holding every parameter of a dtype (launch once, learn the ready order)
         self._rebuilt = False
-        first = [list(range(len(self._params)))]
+        first, _ = R.assign_buckets(self._params, [sys.maxsize])
+        first = [list(ids) for ids in first]
         self._buckets = self._make_buckets(first)
         self._reducer = R.Reducer(self._params, first, self._on_bucket_ready, self._on_finalize)
         self._reducer.set_record_order(True)
         self._stats = {"allreduce_bytes": 0, "launches": 0, "rebuilds": 0}
+        self._install_native_plan()
         self._t_ctor = time.time()
 
     # ------------------------------------------------------------------ construction helpers
@@ -137,7 +140,7 @@ class DistributedDataParallel(nn.Module):
                     f"({int(mine[2])} elements), while rank {r} has {int(v[0])} params ({int(v[2])} elements).")
 
     def _create_arena(self) -> None:
-        from ..ops.collectives import SymmetricArena
+        from ..ops.collectives import make_arena
         st = _group.state() if _group.is_initialized() or dist.is_initialized() else None
         total = sum((p.numel() + 7) // 8 * 8 * 4 for p in self._params)
         # the construction-time broadcast stages parameters AND buffers (as 32-bit words) at once
@@ -152,7 +155,8 @@ class DistributedDataParallel(nn.Module):
                     and st.arena.nbytes >= need and st.arena.group is self.process_group:
                 self._arena = st.arena
             else:
-                self._arena = SymmetricArena(need, self.device, self.process_group)
+                with torch.cuda.device(self.device):
+                    self._arena = make_arena(need, self.device, self.process_group)
                 if st is not None and st.arena is None and not self.gradient_as_bucket_view:
                     st.arena = self._arena
         except Exception as e:  # symmetric memory unavailable: say so loudly, fall back to NCCL
@@ -187,7 +191,8 @@ class DistributedDataParallel(nn.Module):
                 table = coll.TensorTable(list(key), self.device, False, False)
                 tables[key] = table
             table.bind(fast, cur)
-            coll.launch("bcast", self._arena, table, 1.0, cur, root=0, sig_base=4096,
+            coll.launch("bcast", self._arena, table, 1.0, cur, root=0,
+                        sig_base=coll.signal_base(self._arena, f"ddp{id(self)}:bcast", self.max_comm_blocks),
                         max_blocks=self.max_comm_blocks)
         if slow:
             src = dist.get_global_rank(self.process_group, 0)
@@ -230,6 +235,37 @@ class DistributedDataParallel(nn.Module):
         self._assign_grad_views(out)
         return out
 
+    def _install_native_plan(self) -> None:
+        """Hand the C++ reducer everything it needs to launch the fused collective of each bucket itself
+        (no GIL, no Python in the backward hot path).  The Python callbacks stay in charge on CPU / gloo, with
+        the NCCL opt-out, and when the debug handshake or NVTX tracing wrap every launch."""
+        if (not self._use_kernels or self.world_size == 1 or self._debug or _TRACE
+                or os.environ.get("B200DT_PY_REDUCER", "0") not in ("", "0")):
+            self._reducer.clear_native_plan()
+            return
+        from ..ops import collectives as coll
+        from .._lib import lib
+        a = self._arena
+        sig = coll.signal_base(a, f"ddp{id(self)}:buckets", self.max_comm_blocks)
+        self._bucket_sig_base = sig
+        buckets = []
+        for b in self._buckets:
+            t = b.table
+            buckets.append(dict(mode=coll.MODE[b.mode], n_chunks=t.n_chunks, tensor_bf16=int(t.tensor_bf16),
+                                wire_bf16=int(t.wire_bf16), sig_base=sig, grid=t.grid(self.max_comm_blocks),
+                                in_place=int(b.views is not None), stage_base=int(b.stage_base),
+                                scale=1.0 / self.world_size, tensors_dev=t.tensors.data_ptr(),
+                                chunks_dev=t.chunks.data_ptr(), nbytes=int(b.nbytes), param_ids=list(b.param_ids),
+                                numels=list(t.numels), views=list(b.views) if b.views is not None else None))
+            if b.stage_base + t.stage_bytes > a.nbytes:
+                raise RuntimeError(f"bucket {b.index} does not fit the arena")
+        fn = ctypes.cast(lib()._handle.b200dt_coll_launch, ctypes.c_void_p).value
+        self._reducer.set_native_plan(dict(
+            launch_fn=fn, bufs=list(a.buf_ptrs), sigs=list(a.sig_ptrs), mc=int(a.multicast_ptr),
+            status_dev=a.status_words.dev_ptr, status_host=ctypes.addressof(a.status_words._host.contents),
+            rank=a.rank, world=a.world, device=self.device.index, side_stream=self._side_stream.cuda_stream,
+            buckets=buckets))
+
     def _views_possible(self) -> bool:
         wire16 = self.comm_dtype == "bf16"
         return (self.gradient_as_bucket_view and self._use_kernels and self._arena is not None
@@ -267,13 +303,14 @@ class DistributedDataParallel(nn.Module):
             return
         if self.world_size > 1:
             t = torch.tensor(order, dtype=torch.int64, device=self.device if self.device.type == "cuda" else "cpu")
-            dist.broadcast(t, src=0, group=self.process_group)
+            dist.broadcast(t, src=dist.get_global_rank(self.process_group, 0), group=self.process_group)
             order = t.cpu().tolist()
         tensors = [self._params[i] for i in order]
         layout, _ = self._R.assign_buckets(tensors, [FIRST_BUCKET_BYTES, self.bucket_bytes_cap], order)
         self._buckets = self._make_buckets(layout)
         self._reducer.set_buckets(layout)
         self._reducer.set_record_order(False)
+        self._install_native_plan()
         self._rebuilt = True
         self._stats["rebuilds"] += 1
 
@@ -300,7 +337,12 @@ class DistributedDataParallel(nn.Module):
             g = self._params[j].grad
             if g is None:
                 raise RuntimeError(f"parameter {j} has no gradient at bucket launch")
-            grads.append(g if g.is_contiguous() else g.contiguous())
+            if not g.is_contiguous():
+                if self._use_kernels:
+                    raise RuntimeError(f"parameter {j} has a non-contiguous .grad; the fused all-reduce reads gradients "
+                                       "in place (make the gradient contiguous or use allreduce='nccl')")
+                g = g.contiguous()          # fallback path: _on_finalize re-assigns p.grad from the flat bucket
+            grads.append(g)
         self._stats["allreduce_bytes"] += b.nbytes
         self._stats["launches"] += 1
         if self._debug:
@@ -316,6 +358,7 @@ class DistributedDataParallel(nn.Module):
             b.table.bind(grads, self._side_stream)
             with trace_range(f"allreduce[{bi}]"):
                 coll.launch(b.mode, self._arena, b.table, 1.0 / self.world_size, self._side_stream,
+                            sig_base=coll.signal_base(self._arena, f"ddp{id(self)}:buckets", self.max_comm_blocks),
                             max_blocks=self.max_comm_blocks, stage_base=b.stage_base, in_place=b.views is not None)
         else:
             # gloo / NCCL path: flat bucket, pre-scale, async all-reduce (what torch's Reducer does)
@@ -332,6 +375,7 @@ class DistributedDataParallel(nn.Module):
             return
         if self._use_kernels:
             torch.cuda.current_stream(self.device).wait_stream(self._side_stream)
+            self._arena.check_status()          # host-mapped word: no stream is touched
             for b in self._buckets:
                 if b.views is None:
                     continue
@@ -392,6 +436,8 @@ class DistributedDataParallel(nn.Module):
     def get_logging_data(self) -> dict:
         d = dict(self._reducer.stats())
         d.update(self._stats)
+        d["allreduce_bytes"] += d.get("native_bytes", 0)
+        d["launches"] += d.get("native_launches", 0)
         d.update(world_size=self.world_size, rank=self.rank, rebuilt=self._rebuilt,
                  bucket_sizes_mib=[round(b.nbytes / 2**20, 2) for b in self._buckets],
                  bucket_modes=[b.mode for b in self._buckets],
@@ -401,6 +447,7 @@ class DistributedDataParallel(nn.Module):
         return d
 
     def check_comm_status(self) -> None:
-        """Raise if a peer-memory collective timed out (host-side check, synchronises)."""
+        """Raise ``CollectiveTimeout`` if a peer-memory collective gave up waiting for a peer.  Reads a
+        host-mapped word (no synchronisation); the reducer's finalize does the same after every backward."""
         if self._arena is not None:
             self._arena.check_status()

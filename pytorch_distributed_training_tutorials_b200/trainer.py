@@ -78,6 +78,24 @@ class Trainer:
             self.cuda_graph = False
 
     def _run_batch(self, xs, ys):
+        try:
+            return self._run_batch_inner(xs, ys)
+        except RuntimeError as e:
+            self._raise_if_collective_timed_out(e)
+            raise
+
+    def _raise_if_collective_timed_out(self, cause: Optional[BaseException] = None) -> None:
+        """A peer-memory collective that gives up on a peer traps its kernel; what the host sees next is a
+        generic CUDA error.  The status words (pinned host memory) say what really happened."""
+        arena = getattr(self.model, "_arena", None)
+        if arena is None:
+            return
+        try:
+            arena.check_status()
+        except RuntimeError as timeout:
+            raise timeout from cause
+
+    def _run_batch_inner(self, xs, ys):
         if self._fault is not None and self._fault == (_current_rank(), self.global_step):
             raise RuntimeError(f"fault injected on rank {self._fault[0]} at step {self._fault[1]} (B200DT_FAULT_INJECT)")
         if self.cuda_graph:
@@ -109,7 +127,11 @@ class Trainer:
             return float(self.last_loss.item())
         xs = xs.to(self.device, non_blocking=True)
         ys = ys.to(self.device, non_blocking=True)
-        return float(self._run_batch(xs, ys).item())
+        try:
+            return float(self._run_batch(xs, ys).item())
+        except RuntimeError as e:
+            self._raise_if_collective_timed_out(e)
+            raise
 
     def run_batches(self, batches) -> list:
         """Train on an iterable of host ``(xs, ys)`` batches, software-pipelined: the upload of batch

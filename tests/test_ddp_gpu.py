@@ -27,7 +27,7 @@ def _collectives(rank, world, port, out_dir):
     from pytorch_distributed_training_tutorials_b200.ops import collectives as coll
     st = group.init(backend="nccl", rank=rank, world_size=world, master_addr="127.0.0.1", master_port=port)
     dev = st.device
-    arena = coll.SymmetricArena(64 << 20, dev)
+    arena = coll.make_arena(64 << 20, dev)
     modes = ["oneshot", "twoshot"] + (["nvls"] if arena.has_multicast else [])
     torch.manual_seed(1000 + rank)
     sizes = [1, 7, 21, 256, 1000, 4099, 65536, 300001, 2_000_003]
@@ -100,6 +100,17 @@ def test_fused_collectives_match_nccl(tmp_path):
     w = _world()
     spawn(_collectives, args=(w, group.find_free_port(), str(tmp_path)), nprocs=w)
     assert all((tmp_path / f"ok{r}").exists() for r in range(w))
+    # where the driver offers multicast the library's own arena must have bound it, i.e. the multimem
+    # (NVLS) kernels really ran above instead of being skipped
+    if _multicast_supported():
+        assert "nvls" in (tmp_path / "ok0").read_text()
+
+
+def _multicast_supported():
+    from pytorch_distributed_training_tutorials_b200._lib import lib
+    h = lib()._handle
+    h.b200dt_multicast_supported.argtypes = [__import__("ctypes").c_int]
+    return int(h.b200dt_multicast_supported(0)) == 1
 
 
 def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype, views=False):
@@ -112,8 +123,15 @@ def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype, views=False):
         torch.manual_seed(5)
         return torch.nn.Sequential(torch.nn.Linear(64, 512), torch.nn.ReLU(), torch.nn.Linear(512, 2048),
                                    torch.nn.ReLU(), torch.nn.BatchNorm1d(2048), torch.nn.Linear(2048, 10)).to(dev)
-    mine = DDP(make(), device_ids=[dev.index], allreduce=mode, comm_dtype=comm_dtype, bucket_cap_mb=1,
-               gradient_as_bucket_view=views)
+    try:
+        mine = DDP(make(), device_ids=[dev.index], allreduce=mode, comm_dtype=comm_dtype, bucket_cap_mb=1,
+                   gradient_as_bucket_view=views)
+    except RuntimeError as e:
+        if mode == "nvls" and "no multicast" in str(e):
+            group.destroy()
+            open(os.path.join(out_dir, f"ok{rank}"), "w").write("nomc")
+            return
+        raise
     ref = torch.nn.parallel.DistributedDataParallel(make(), device_ids=[dev.index], bucket_cap_mb=1)
     o1 = torch.optim.SGD(mine.parameters(), lr=0.05); o2 = torch.optim.SGD(ref.parameters(), lr=0.05)
     g = torch.Generator(device="cpu").manual_seed(11 + rank)
@@ -152,11 +170,17 @@ def _ddp_vs_torch(rank, world, port, out_dir, mode, comm_dtype, views=False):
 
 
 @needs2
-@pytest.mark.parametrize("mode,comm_dtype", [("auto", "fp32"), ("oneshot", "fp32"), ("twoshot", "fp32"), ("auto", "bf16")])
+@pytest.mark.parametrize("mode,comm_dtype", [("auto", "fp32"), ("oneshot", "fp32"), ("twoshot", "fp32"), ("auto", "bf16"),
+                                             ("nvls", "fp32"), ("nvls", "bf16")])
 def test_ddp_matches_torch_ddp(tmp_path, mode, comm_dtype):
     w = _world()
     spawn(_ddp_vs_torch, args=(w, group.find_free_port(), str(tmp_path), mode, comm_dtype), nprocs=w)
     assert all((tmp_path / f"ok{r}").exists() for r in range(w))
+    if mode == "nvls":
+        ran = (tmp_path / "ok0").read_text() != "nomc"
+        assert ran or not _multicast_supported(), "the driver offers multicast but the arena did not bind it"
+        if not ran:
+            pytest.skip("no NVLS multicast on this box")
 
 
 def _ddp_views_native(rank, world, port, out_dir):
@@ -207,3 +231,53 @@ def test_ddp_gradient_as_bucket_view(tmp_path):
     w = _world()
     spawn(_ddp_vs_torch, args=(w, group.find_free_port(), str(tmp_path), "auto", "fp32", True), nprocs=w)
     assert all((tmp_path / f"ok{r}").exists() for r in range(w))
+
+
+def _timeout_child(rank, world, port, out_dir):
+    import json
+    import time
+    from pytorch_distributed_training_tutorials_b200._lib import lib
+    from pytorch_distributed_training_tutorials_b200.ops import collectives as coll
+    st = group.init(backend="nccl", rank=rank, world_size=world, master_addr="127.0.0.1", master_port=port)
+    dev = st.device
+    arena = coll.make_arena(1 << 20, dev)
+    lib()._handle.b200dt_set_coll_timeout_ms.argtypes = [__import__("ctypes").c_longlong]
+    lib()._handle.b200dt_set_coll_timeout_ms(1500)
+    x = torch.ones(1000, device=dev)
+    coll.all_reduce_([x], arena)                    # a healthy collective first
+    torch.cuda.synchronize(dev)
+    assert float(x[0]) == world
+    dist.barrier(device_ids=[dev.index])
+    if rank == world - 1:
+        os._exit(0)                                 # this rank "dies" before the next collective
+    t0 = time.time()
+    coll.all_reduce_([x], arena)
+    raised = False
+    try:
+        torch.cuda.synchronize(dev)
+    except RuntimeError:
+        raised = True                               # the kernel trapped: nothing was reduced from partial data
+    msg = None
+    try:
+        arena.check_status()
+    except coll.CollectiveTimeout as e:
+        msg = str(e)
+    with open(os.path.join(out_dir, f"t{rank}.json"), "w") as f:
+        json.dump({"raised": raised, "msg": msg, "elapsed": time.time() - t0}, f)
+        f.flush()
+        os.fsync(f.fileno())
+    os._exit(0)                                     # the CUDA context is gone: skip every destructor
+
+
+@needs2
+def test_dead_peer_is_detected_within_the_time_limit(tmp_path):
+    """One rank exits between two collectives: the survivors' kernels give up after the configured limit, trap
+    (no gradient is ever built from partial data), and the host reads who was missing from the status words."""
+    import json
+    w = _world()
+    spawn(_timeout_child, args=(w, group.find_free_port(), str(tmp_path)), nprocs=w)
+    for r in range(w - 1):
+        rec = json.loads((tmp_path / f"t{r}.json").read_text())
+        assert rec["raised"], rec
+        assert rec["msg"] is not None and "waiting for rank" in rec["msg"], rec
+        assert rec["elapsed"] < 20, rec
