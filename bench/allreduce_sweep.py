@@ -57,17 +57,28 @@ def main():
         (xv,) = coll.stage_views(arena, table, [(n,)])
         xv.copy_(x)
         table.bind([xv], stream)
-        m = "nvls" if arena.has_multicast else "twoshot"
-        row[m + "_inplace_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks,
-                                                           in_place=True), iters, dev)
+        for m in (["twoshot", "nvls"] if arena.has_multicast else ["twoshot"]):
+            row[m + "_inplace_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks,
+                                                               in_place=True), iters, dev)
         if size >= (1 << 20):
             table = coll.TensorTable([n], dev, True, False, target_blocks=args.blocks)
             table.bind([x], stream)
-            m = "nvls" if arena.has_multicast else "twoshot"
-            row[m + "_bf16wire_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks), iters, dev)
+            for m in (["twoshot", "nvls"] if arena.has_multicast else ["twoshot"]):
+                row[m + "_bf16wire_ms"] = timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=args.blocks), iters, dev)
         arena.check_status()
         rows.append(row)
         size *= 4
+    probe = {}
+    if arena.has_multicast and max_bytes >= (64 << 20):
+        # how many CTAs does the NVLS kernel want?  (64 MiB fp32 in place)
+        n = (64 << 20) // 4
+        stream = torch.cuda.current_stream(dev)
+        for blocks in (16, 32, 64, 128, 256):
+            table = coll.TensorTable([n], dev, False, False, target_blocks=blocks)
+            (xv,) = coll.stage_views(arena, table, [(n,)])
+            table.bind([xv], stream)
+            probe[blocks] = {m: timed(lambda: coll.launch(m, arena, table, 1.0, stream, max_blocks=blocks, in_place=True), 10, dev)
+                             for m in ("twoshot", "nvls")}
     if rank == 0:
         f = 2 * (world - 1) / world
         keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_inplace_ms", "nvls_inplace_ms",
@@ -82,8 +93,27 @@ def main():
                 else:
                     cells.append("-")
             print(f"| {r['bytes']} | " + " | ".join(cells) + " |")
+        # roofline: bytes every GPU must push through its 900 GB/s/direction NVLink port
+        #   two-shot: 2 S (N-1)/N   (== busbw definition)      NVLS: S (N+1)/N   (switch reduces / fans out)
+        R = 900e9
+        print()
+        print("| bytes | best in-place kernel | us | % of link bound (900 GB/s) | % of measured peer-copy rate (770 GB/s) | vs NCCL |")
+        print("|---|---|---|---|---|---|")
+        for r in rows:
+            cands = {k: r[k] for k in ("twoshot_inplace_ms", "nvls_inplace_ms") if k in r}
+            k = min(cands, key=cands.get)
+            t = cands[k] * 1e-3
+            need = r["bytes"] * ((world + 1) / world if k.startswith("nvls") else f)
+            print(f"| {r['bytes']} | {k[:-11]} | {t * 1e6:.1f} | {100 * need / R / t:.1f} | {100 * need / 770e9 / t:.1f} | "
+                  f"{r['nccl_ms'] * 1e-3 / t:.2f}x |")
+        if probe:
+            print()
+            print("64 MiB fp32 in place, ms by CTA count: " + "; ".join(
+                f"{b}: twoshot {v['twoshot']:.3f} nvls {v['nvls']:.3f}" for b, v in probe.items()))
         os.makedirs("gpurun_out", exist_ok=True)
-        json.dump({"world": world, "multicast": arena.has_multicast, "rows": rows}, open(f"gpurun_out/allreduce_sweep_{world}.json", "w"), indent=1)
+        json.dump({"world": world, "cta_probe_64MiB_ms": probe, "multicast": arena.has_multicast, "arena": arena.flavour,
+                   "multicast_error": arena.multicast_error, "rows": rows},
+                  open(f"gpurun_out/allreduce_sweep_{world}.json", "w"), indent=1)
     group.destroy()
 
 

@@ -406,47 +406,74 @@ coll_kernel(const __grid_constant__ CollArgs a) {
       const int per = (groups + a.world - 1) / a.world;      // groups owned by each rank
       const int g0 = a.rank * per;
       const int g1 = min(groups, g0 + per);
+      if (kMode == kNvls) {
+        // The switch adds (multimem.ld_reduce) and fans out (multimem.st).  A load-reduce is a round trip
+        // through the NVSwitch, so several of them are kept in flight per thread before the first store.
+        constexpr int U = 4;
+        char* mcs = reinterpret_cast<char*>(a.mc) + a.stage_base;
+        const float post = a.in_place ? a.scale : 1.f;
+        for (int gb = g0 + threadIdx.x; gb < g1; gb += U * blockDim.x) {
+          if (a.wire_bf16) {
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int g = gb + u * blockDim.x;
+              if (g < g1) v[u] = multimem_ld_reduce_bf16x8(reinterpret_cast<__nv_bfloat16*>(mcs) + ch.stage_off + (long long)g * 8);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int g = gb + u * blockDim.x;
+              if (g >= g1) continue;
+              if (post != 1.f) {
+                float f[8];
+                unpack8(v[u], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] *= post;
+                v[u] = pack8(f);
+              }
+              multimem_st_v4(reinterpret_cast<__nv_bfloat16*>(mcs) + ch.stage_off + (long long)g * 8, v[u]);
+            }
+          } else {
+            uint4 v0[U], v1[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int g = gb + u * blockDim.x;
+              if (g < g1) {
+                float* p = reinterpret_cast<float*>(mcs) + ch.stage_off + (long long)g * 8;
+                v0[u] = multimem_ld_reduce_f32x4(p);
+                v1[u] = multimem_ld_reduce_f32x4(p + 4);
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int g = gb + u * blockDim.x;
+              if (g >= g1) continue;
+              float* p = reinterpret_cast<float*>(mcs) + ch.stage_off + (long long)g * 8;
+              if (post != 1.f) {
+                v0[u] = make_uint4(__float_as_uint(__uint_as_float(v0[u].x) * post), __float_as_uint(__uint_as_float(v0[u].y) * post),
+                                   __float_as_uint(__uint_as_float(v0[u].z) * post), __float_as_uint(__uint_as_float(v0[u].w) * post));
+                v1[u] = make_uint4(__float_as_uint(__uint_as_float(v1[u].x) * post), __float_as_uint(__uint_as_float(v1[u].y) * post),
+                                   __float_as_uint(__uint_as_float(v1[u].z) * post), __float_as_uint(__uint_as_float(v1[u].w) * post));
+              }
+              multimem_st_v4(p, v0[u]);
+              multimem_st_v4(p + 4, v1[u]);
+            }
+          }
+        }
+        continue;
+      }
       for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
         const long long e = ch.stage_off + (long long)g * 8;
-        if (kMode == kNvls) {
-          char* mcs = reinterpret_cast<char*>(a.mc) + a.stage_base;
-          const float post = a.in_place ? a.scale : 1.f;
-          if (a.wire_bf16) {
-            __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(mcs) + e;
-            uint4 v = multimem_ld_reduce_bf16x8(p);
-            if (post != 1.f) {
-              float f[8];
-              unpack8(v, f);
+        float acc[8];
+        reduce_group(a, e, acc);
+        if (a.in_place) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] *= post;
-              v = pack8(f);
-            }
-            multimem_st_v4(p, v);
-          } else {
-            float* p = reinterpret_cast<float*>(mcs) + e;
-            uint4 v0 = multimem_ld_reduce_f32x4(p);
-            uint4 v1 = multimem_ld_reduce_f32x4(p + 4);
-            if (post != 1.f) {
-              v0 = make_uint4(__float_as_uint(__uint_as_float(v0.x) * post), __float_as_uint(__uint_as_float(v0.y) * post),
-                              __float_as_uint(__uint_as_float(v0.z) * post), __float_as_uint(__uint_as_float(v0.w) * post));
-              v1 = make_uint4(__float_as_uint(__uint_as_float(v1.x) * post), __float_as_uint(__uint_as_float(v1.y) * post),
-                              __float_as_uint(__uint_as_float(v1.z) * post), __float_as_uint(__uint_as_float(v1.w) * post));
-            }
-            multimem_st_v4(p, v0);
-            multimem_st_v4(p + 4, v1);
-          }
-        } else {
-          float acc[8];
-          reduce_group(a, e, acc);
-          if (a.in_place) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] *= a.scale;
-          }
-#pragma unroll
-          for (int r = 0; r < B200DT_MAX_WORLD; ++r)
-            if (r < a.world)
-              store8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, e, a.wire_bf16, acc);
+          for (int j = 0; j < 8; ++j) acc[j] *= a.scale;
         }
+#pragma unroll
+        for (int r = 0; r < B200DT_MAX_WORLD; ++r)
+          if (r < a.world)
+            store8_stage(reinterpret_cast<char*>(a.bufs[r]) + a.stage_base, e, a.wire_bf16, acc);
       }
     }
     if (a.world > 1) block_barrier(a);

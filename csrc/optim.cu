@@ -25,7 +25,11 @@ template <bool kAdam>
 __global__ void __launch_bounds__(256)
 multi_opt_kernel(const TensorMeta* __restrict__ meta, const int2* __restrict__ chunks, float lr,
                  float beta1, float beta2, float eps, float wd, float bc1, float bc2_rsqrt,
-                 float gscale, int zero_grad) {
+                 float gscale, int zero_grad, const float* __restrict__ bc_dev) {
+  if (kAdam && bc_dev != nullptr) {       // capturable Adam: the bias corrections follow a device-side step count
+    bc1 = bc_dev[0];
+    bc2_rsqrt = bc_dev[1];
+  }
   const int2 ch = chunks[blockIdx.x];
   const TensorMeta m = meta[ch.x];
   const long long begin = ch.y;
@@ -89,6 +93,15 @@ multi_opt_kernel(const TensorMeta* __restrict__ meta, const int2* __restrict__ c
   }
 }
 
+// step += 1 and the two bias corrections derived from it, all on the device: what lets Adam live in a CUDA graph
+// (the host-side step count of the plain entry point would be frozen into the captured launch).
+__global__ void adam_bump_kernel(float* step, float* bc, float beta1, float beta2) {
+  const double t = (double)step[0] + 1.0;
+  step[0] = (float)t;
+  bc[0] = (float)(1.0 - pow((double)beta1, t));
+  bc[1] = (float)(1.0 / sqrt(1.0 - pow((double)beta2, t)));
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -98,7 +111,7 @@ extern "C" int b200dt_multi_sgd(const long long* meta, const int* chunks, int n_
   if (n_chunks <= 0) return 0;
   multi_opt_kernel<false><<<n_chunks, 256, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const TensorMeta*>(meta), reinterpret_cast<const int2*>(chunks), lr, 0.f, 0.f,
-      0.f, weight_decay, 1.f, 1.f, grad_scale, zero_grad);
+      0.f, weight_decay, 1.f, 1.f, grad_scale, zero_grad, nullptr);
   return (int)cudaGetLastError();
 }
 
@@ -110,6 +123,20 @@ extern "C" int b200dt_multi_adam(const long long* meta, const int* chunks, int n
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   multi_opt_kernel<true><<<n_chunks, 256, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const TensorMeta*>(meta), reinterpret_cast<const int2*>(chunks), lr, beta1,
-      beta2, eps, weight_decay, (float)bc1, (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
+      beta2, eps, weight_decay, (float)bc1, (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad, nullptr);
+  return (int)cudaGetLastError();
+}
+
+// Adam whose step count lives on the device: step_state = {step, bc1, 1/sqrt(bc2)} (3 floats; step is
+// incremented by the call).  Two launches, both capturable in a CUDA graph.
+extern "C" int b200dt_multi_adam_capturable(const long long* meta, const int* chunks, int n_chunks, float lr,
+                                            float beta1, float beta2, float eps, float weight_decay,
+                                            float* step_state, float grad_scale, int zero_grad, void* stream) {
+  if (step_state == nullptr) return -3;
+  adam_bump_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_state, step_state + 1, beta1, beta2);
+  if (n_chunks <= 0) return (int)cudaGetLastError();
+  multi_opt_kernel<true><<<n_chunks, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const TensorMeta*>(meta), reinterpret_cast<const int2*>(chunks), lr, beta1,
+      beta2, eps, weight_decay, 1.f, 1.f, grad_scale, zero_grad, step_state + 1);
   return (int)cudaGetLastError();
 }

@@ -108,6 +108,31 @@ p2p_gather_kernel(const unsigned char* __restrict__ src, unsigned char* __restri
   }
 }
 
+// Up to eight independent (src, dst, bytes) segments copied by ONE launch: the scatter of DataParallel
+// (root slices -> one buffer per peer, stores over NVLink), its gather (peer buffers -> slices of the root
+// tensor, loads over NVLink) and the slice hand-out of the two-level broadcast are all this kernel.
+struct SegArgs {
+  const unsigned char* src[8];
+  unsigned char* dst[8];
+  long long begin[9];       // prefix sums of the segment sizes in 16-byte vectors (vec) or bytes (!vec)
+  int n;
+};
+
+__global__ void __launch_bounds__(512)
+p2p_multi_copy_kernel(SegArgs a, int vec) {
+  const long long total = a.begin[a.n];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += stride) {
+    int s = 0;
+#pragma unroll
+    for (int k = 1; k < 8; ++k)
+      if (k < a.n && i >= a.begin[k]) s = k;
+    const long long off = i - a.begin[s];
+    if (vec) st_v4(reinterpret_cast<uint4*>(a.dst[s]) + off, ld_nc_v4(reinterpret_cast<const uint4*>(a.src[s]) + off));
+    else a.dst[s][off] = a.src[s][off];
+  }
+}
+
 static int blocks_for(long long nvec, int cap) {
   long long b = (nvec + 511) / 512;
   if (b > cap) b = cap;
@@ -172,6 +197,28 @@ extern "C" int b200dt_p2p_gather_rows(const void* src, void* dst_peer, long long
   p2p_gather_kernel<<<blocks_for(nbytes / 16, 32), 512, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const unsigned char*>(src), reinterpret_cast<unsigned char*>(dst_peer), nbytes,
       partial_peer, is_f32);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200dt_p2p_multi_copy(const uint64_t* srcs_host, const uint64_t* dsts_host,
+                                     const long long* nbytes_host, int n, void* stream) {
+  if (n <= 0) return 0;
+  if (n > 8) return -3;
+  SegArgs a{};
+  bool vec = true;
+  for (int k = 0; k < n; ++k) {
+    if (nbytes_host[k] < 0) return -3;
+    vec = vec && ((srcs_host[k] & 15) == 0) && ((dsts_host[k] & 15) == 0) && (nbytes_host[k] % 16 == 0);
+  }
+  a.n = n;
+  a.begin[0] = 0;
+  for (int k = 0; k < n; ++k) {
+    a.src[k] = reinterpret_cast<const unsigned char*>(srcs_host[k]);
+    a.dst[k] = reinterpret_cast<unsigned char*>(dsts_host[k]);
+    a.begin[k + 1] = a.begin[k] + (vec ? nbytes_host[k] / 16 : nbytes_host[k]);
+  }
+  if (a.begin[n] == 0) return 0;
+  p2p_multi_copy_kernel<<<blocks_for(a.begin[n], 64), 512, 0, (cudaStream_t)stream>>>(a, vec ? 1 : 0);
   return (int)cudaGetLastError();
 }
 

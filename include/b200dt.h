@@ -177,6 +177,12 @@ int b200dt_multi_sgd(const long long* meta, const int* chunks, int n_chunks, flo
 int b200dt_multi_adam(const long long* meta, const int* chunks, int n_chunks, float lr, float beta1,
                       float beta2, float eps, float weight_decay, int step, float grad_scale,
                       int zero_grad, void* stream);
+/* Same update with the step count on the device (torch's Adam(capturable=True)): step_state = 3 floats
+ * {step, 1 - beta1^step, 1/sqrt(1 - beta2^step)}; the call increments step first. Capturable in a CUDA graph,
+ * which the reference's DataParallel loop (01.data_parallel.ipynb:287,478-487) needs to be replayed from one. */
+int b200dt_multi_adam_capturable(const long long* meta, const int* chunks, int n_chunks, float lr, float beta1,
+                                 float beta2, float eps, float weight_decay, float* step_state,
+                                 float grad_scale, int zero_grad, void* stream);
 
 /* ---------------------------------------------------------------- multi-process collectives
  * Replaces the NCCL all-reduce / broadcast issued by DistributedDataParallel (ddp_gpus.py:32,38)
@@ -253,6 +259,11 @@ int b200dt_p2p_broadcast(const void* src, const uint64_t* dsts_host, int ndst, l
 /* dst (current device) = sum of nsrc peer buffers (fp32), scaled. */
 int b200dt_p2p_reduce_f32(float* dst, const uint64_t* srcs_host, int nsrc, long long n,
                           float scale, int accumulate, void* stream);
+/* n <= 8 independent copies dst[k][0..nbytes[k]) = src[k][...] in ONE launch on the current device; any of
+ * the pointers may be peer memory. DataParallel's scatter (root slices -> peers), gather (peers -> slices
+ * of the root tensor) and the slice hand-out of its two-level broadcast. Host arrays. */
+int b200dt_p2p_multi_copy(const uint64_t* srcs_host, const uint64_t* dsts_host, const long long* nbytes_host,
+                          int n, void* stream);
 /* Copy rows [row0, row0+rows) x row_bytes from the current device into dst (peer) and, if
  * partial != NULL, also add sum(src) (fp32 data) into *partial: gather fused with the loss sum. */
 int b200dt_p2p_gather_rows(const void* src, void* dst_peer, long long nbytes, float* partial_peer,

@@ -72,6 +72,7 @@ _SIGS = {
     "b200dt_ce_index_loss": [vp, vp, vp, vp, i32, i32, f32, i32, vp, vp],
     "b200dt_multi_sgd": [vp, vp, i32, f32, f32, f32, i32, vp],
     "b200dt_multi_adam": [vp, vp, i32, f32, f32, f32, f32, f32, i32, f32, i32, vp],
+    "b200dt_multi_adam_capturable": [vp, vp, i32, f32, f32, f32, f32, f32, vp, f32, i32, vp],
     "b200dt_coll_launch": [i32, vp, vp, u64, i32, i32, i32, vp, vp, i32, i64, i32, i32, f32, i32,
                            i32, vp, i32, vp],
     "b200dt_scale_cast": [vp, vp, i64, f32, i32, vp],
@@ -81,6 +82,7 @@ _SIGS = {
     "b200dt_p2p_broadcast": [vp, vp, i32, i64, vp],
     "b200dt_p2p_reduce_f32": [vp, vp, i32, i64, f32, i32, vp],
     "b200dt_p2p_gather_rows": [vp, vp, i64, vp, i32, vp],
+    "b200dt_p2p_multi_copy": [vp, vp, vp, i32, vp],
     "b200dt_memcpy_h2d_async": [vp, vp, i64, vp],
 }
 

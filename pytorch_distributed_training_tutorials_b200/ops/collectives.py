@@ -172,7 +172,13 @@ class SymmetricArena:
         self.buf = self.sig = None
 
 
-def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> str:
+# Measured on 4 x B200 (profiles/allreduce_sweep.md): with fp32 on the wire the two-shot kernel beats the NVLS
+# kernel at every size (1 GiB in place: 2.42 vs 3.72 ms), with bf16 on the wire NVLS is the fastest variant
+# from 4 MiB up.  "auto" follows the measurements; B200DT_PREFER_NVLS=1/0 overrides it.
+NVLS_MIN_BYTES_BF16 = 4 << 20
+
+
+def pick_mode(nbytes: int, arena, requested: str = "auto", wire_bf16: bool = False) -> str:
     if requested != "auto":
         if requested == "nvls" and not arena.has_multicast:
             raise RuntimeError("allreduce='nvls' requested but the arena has no multicast mapping "
@@ -182,7 +188,11 @@ def pick_mode(nbytes: int, arena: SymmetricArena, requested: str = "auto") -> st
     # messages, and the break-even shrinks with the number of peers (measured: profiles/)
     if nbytes <= (ONESHOT_MAX_BYTES if arena.world <= 2 else 16 * 1024):
         return "oneshot"
-    return "nvls" if arena.has_multicast else "twoshot"
+    prefer = os.environ.get("B200DT_PREFER_NVLS", "")
+    if arena.has_multicast and arena.world > 2:
+        if prefer == "1" or (prefer != "0" and wire_bf16 and nbytes >= NVLS_MIN_BYTES_BF16):
+            return "nvls"
+    return "twoshot"
 
 
 class TensorTable:
@@ -302,7 +312,7 @@ def all_reduce_(tensors: List[torch.Tensor], arena: SymmetricArena, mode: str = 
     tb16 = tensors[0].dtype == torch.bfloat16
     table = TensorTable([t.numel() for t in tensors], dev, wire_bf16, tb16, target_blocks=max_blocks)
     table.bind(tensors, stream)
-    m = pick_mode(table.stage_bytes, arena, mode)
+    m = pick_mode(table.stage_bytes, arena, mode, table.wire_bf16)
     launch(m, arena, table, scale, stream, max_blocks=max_blocks)
 
 

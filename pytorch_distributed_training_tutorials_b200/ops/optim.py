@@ -109,6 +109,10 @@ class _FusedBase(Optimizer):
                     p._b200_shadow = (p._version, sh)
 
     def _publish_shadows(self, params) -> None:
+        # the kernel wrote the parameters behind autograd's back: bump their version counters (what an in-place
+        # torch op would have done) so that version-keyed caches -- DataParallel's replica cache, the bf16 operand
+        # shadows -- notice, then re-publish the shadows the kernel has just refreshed under the new version
+        torch.autograd.graph.increment_version(list(params))
         for p in params:
             sh = self._shadows.get(id(p))
             if sh is not None:
@@ -160,11 +164,55 @@ class FusedAdam(_FusedBase):
     """Adam (Kingma & Ba) with torch's default update rule (no amsgrad)."""
 
     def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, fuse_zero_grad: bool = False, bf16_shadow: bool = True) -> None:
+                 weight_decay: float = 0.0, fuse_zero_grad: bool = False, bf16_shadow: bool = True,
+                 capturable: bool = False) -> None:
+        """``capturable=True`` (like ``torch.optim.Adam(capturable=True)``): the step count lives on the device
+        (``state[p]["step"]`` is a CUDA tensor shared by the parameters of a group on one device), so ``step()``
+        can be captured in a CUDA graph and replayed -- ``Trainer(cuda_graph=True)`` / ``GraphedDataParallel``
+        with the reference's Adam loop (01.data_parallel.ipynb:287)."""
         if lr < 0:
             raise ValueError(f"Invalid learning rate: {lr}")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay),
                          fuse_zero_grad, bf16_shadow)
+        self.capturable = capturable
+        self._step_state: Dict[tuple, torch.Tensor] = {}
+
+    def _step_capturable(self, grad_scale: float):
+        for gi, group in enumerate(self.param_groups):
+            b1, b2 = group["betas"]
+            by_dev, slow = self._cuda_groups(group)
+            if slow:
+                raise RuntimeError("capturable FusedAdam needs contiguous fp32 CUDA parameters and gradients")
+            for dev, ps in by_dev.items():
+                ss = self._step_state.get((gi, dev))
+                if ss is None:
+                    if torch.cuda.is_current_stream_capturing():
+                        raise RuntimeError("run one eager step() (or call init_state()) before capturing FusedAdam")
+                    # resume from a host-side count if this optimizer was stepped / loaded before
+                    t0 = max([float(self.state[p]["step"]) for p in ps if "step" in self.state[p]] or [0.0])
+                    ss = torch.tensor([t0, 0.0, 0.0], dtype=torch.float32, device=dev)
+                    self._step_state[(gi, dev)] = ss
+                rows = []
+                for p in ps:
+                    st = self.state[p]
+                    if "exp_avg" not in st:
+                        if torch.cuda.is_current_stream_capturing():
+                            raise RuntimeError("run one eager step() before capturing FusedAdam")
+                        st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                        st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    st["step"] = ss[0]                                     # a view: always the device-side count
+                    sh = self._shadow_for(p)
+                    rows.append([p.data_ptr(), p.grad.data_ptr(), sh.data_ptr() if sh is not None else 0,
+                                 p.numel(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), 0, 0])
+                tab = self._tables.setdefault((gi, dev), _DeviceTable(dev))
+                tab.update(rows)
+                with torch.cuda.device(dev):
+                    check(lib().b200dt_multi_adam_capturable(ptr(tab.meta), ptr(tab.chunks), tab.n_chunks, group["lr"],
+                                                             b1, b2, group["eps"], group["weight_decay"], ptr(ss),
+                                                             grad_scale, int(self.fuse_zero_grad), stream_ptr(dev)),
+                          "multi_adam_capturable")
+                self._publish_shadows(ps)
+        self._grads_cleared = self.fuse_zero_grad
 
     @torch.no_grad()
     def step(self, closure=None, grad_scale: float = 1.0):
@@ -172,9 +220,12 @@ class FusedAdam(_FusedBase):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        if self.capturable:
+            self._step_capturable(grad_scale)
+            return loss
         if torch.cuda.is_available() and torch.cuda.is_current_stream_capturing():
-            raise RuntimeError("FusedAdam keeps its step count on the host and cannot be captured in a CUDA "
-                               "graph; use FusedSGD under GraphedTrainStep")
+            raise RuntimeError("this FusedAdam keeps its step count on the host; construct it with "
+                               "capturable=True to capture step() in a CUDA graph")
         for gi, group in enumerate(self.param_groups):
             b1, b2 = group["betas"]
             t = None

@@ -65,7 +65,27 @@ def _copy_to(t: torch.Tensor, dev: torch.device) -> torch.Tensor:
     return t.to(dev, non_blocking=True)
 
 
+def _multi_copy(srcs: Sequence[torch.Tensor], dsts: Sequence[torch.Tensor], on: torch.device) -> None:
+    """``dsts[k].copy_(srcs[k])`` for up to 8 contiguous same-size pairs as ONE kernel on ``on``'s current stream
+    (peer loads / stores over NVLink; ``csrc/p2p.cu`` ``p2p_multi_copy_kernel``)."""
+    import ctypes
+    n = len(srcs)
+    nbytes = (ctypes.c_longlong * n)(*[t.numel() * t.element_size() for t in srcs])
+    with torch.cuda.device(on):
+        _lib.check(_lib.lib().b200dt_p2p_multi_copy(_lib.u64_array([t.data_ptr() for t in srcs]),
+                                                    _lib.u64_array([t.data_ptr() for t in dsts]), nbytes, n,
+                                                    _lib.stream_ptr(on)), "p2p_multi_copy")
+
+
+def _kernel_scatter_ok(x: torch.Tensor, devices: Sequence[torch.device], dim: int) -> bool:
+    return (x.is_cuda and dim == 0 and x.dim() >= 1 and x.is_contiguous() and x.shape[0] > 0 and len(devices) <= 8
+            and _is_cuda(devices))
+
+
 class Scatter(torch.autograd.Function):
+    """Split dim 0 into per-device chunks.  CUDA: the chunks of every peer leave the source device in ONE
+    store kernel (K5; torch issues one cudaMemcpyPeerAsync per chunk, torch:nn/parallel/comm.py:209)."""
+
     @staticmethod
     def forward(ctx, devices, dim, x):
         devices = [_dev(d) for d in devices]
@@ -74,12 +94,30 @@ class Scatter(torch.autograd.Function):
         sizes = chunk_sizes(x.shape[dim], len(devices))
         pieces = torch.split(x, sizes, dim=dim) if x.shape[dim] > 0 else (x,)
         outs = []
-        for piece, d in zip(pieces, devices):
-            if d == x.device:
-                outs.append(piece.contiguous() if d.type == "cuda" else piece)
-            else:
-                # stream-ordered peer copy: the chunk is ready on d's current stream
-                outs.append(_copy_to(piece.contiguous(), d))
+        if _kernel_scatter_ok(x, devices, dim) and len(pieces) > 1:
+            ensure_peer_access(list(dict.fromkeys([x.device] + devices[:len(pieces)])))
+            srcs, dsts = [], []
+            for piece, d in zip(pieces, devices):
+                if d == x.device:
+                    outs.append(piece)                       # a view: nothing moves
+                    continue
+                with torch.cuda.device(d):
+                    o = torch.empty(piece.shape, dtype=x.dtype, device=d)
+                _wait_current(x.device, d)                   # d's allocator may still have work queued on that block
+                outs.append(o)
+                srcs.append(piece); dsts.append(o)
+            if srcs:
+                _multi_copy(srcs, dsts, x.device)
+                for o in dsts:
+                    _wait_current(o.device, x.device)        # the chunk is ready on d's current stream
+                    o.record_stream(torch.cuda.current_stream(x.device))
+        else:
+            for piece, d in zip(pieces, devices):
+                if d == x.device:
+                    outs.append(piece.contiguous() if d.type == "cuda" else piece)
+                else:
+                    # host input or a non-leading dimension: stream-ordered copy per chunk
+                    outs.append(_copy_to(piece.contiguous(), d))
         ctx.out_devices = [o.device for o in outs]
         return tuple(outs)
 
@@ -89,6 +127,9 @@ class Scatter(torch.autograd.Function):
 
 
 class Gather(torch.autograd.Function):
+    """Concatenate per-device outputs on ``target``.  CUDA: the target PULLS every peer's rows straight into its
+    slice of the result in ONE kernel (K6; no staging copies, no ``cat``)."""
+
     @staticmethod
     def forward(ctx, target, dim, *xs):
         target = _dev(target)
@@ -101,6 +142,25 @@ class Gather(torch.autograd.Function):
             xs = tuple(x.view(1) for x in xs)
             _warn_scalar()
         ctx.sizes = [x.shape[dim] for x in xs]
+        fast = (target.type == "cuda" and dim == 0 and 1 < len(xs) <= 8 and all(x.is_cuda and x.dim() >= 1 for x in xs)
+                and all(x.dtype == xs[0].dtype and x.shape[1:] == xs[0].shape[1:] for x in xs))
+        if fast:
+            ensure_peer_access(list(dict.fromkeys([target] + [x.device for x in xs])))
+            with torch.cuda.device(target):
+                out = torch.empty((sum(ctx.sizes),) + tuple(xs[0].shape[1:]), dtype=xs[0].dtype, device=target)
+            srcs, dsts, off = [], [], 0
+            for x in xs:
+                n = x.shape[0]
+                if n:
+                    xc = x.contiguous()
+                    if xc.device != target:
+                        _wait_current(target, xc.device)
+                        xc.record_stream(torch.cuda.current_stream(target))
+                    srcs.append(xc); dsts.append(out[off:off + n])
+                off += n
+            if srcs:
+                _multi_copy(srcs, dsts, target)
+            return out
         moved = []
         for x in xs:
             if x.device != target and x.is_cuda:
@@ -110,6 +170,26 @@ class Gather(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        devs = ctx.src_devices
+        if g.is_cuda and ctx.dim == 0 and g.is_contiguous() and len(devs) > 1 and _is_cuda(devs) and len(devs) <= 8:
+            # scatter of the gradient: one store kernel on the target for all peers
+            pieces = torch.split(g, ctx.sizes, dim=0)
+            ensure_peer_access(list(dict.fromkeys([g.device] + devs)))
+            outs, srcs, dsts = [], [], []
+            for p, d in zip(pieces, devs):
+                if d == g.device:
+                    outs.append(p)
+                    continue
+                with torch.cuda.device(d):
+                    o = torch.empty(p.shape, dtype=g.dtype, device=d)
+                _wait_current(g.device, d)
+                outs.append(o); srcs.append(p); dsts.append(o)
+            if srcs:
+                _multi_copy(srcs, dsts, g.device)
+                for o in dsts:
+                    _wait_current(o.device, g.device)
+                    o.record_stream(torch.cuda.current_stream(g.device))
+            return (None, None) + tuple(o.view(()) if ctx.scalar else o for o in outs)
         pieces = torch.split(g, ctx.sizes, dim=ctx.dim)
         outs = []
         for p, d in zip(pieces, ctx.src_devices):
@@ -130,11 +210,22 @@ def _warn_scalar() -> None:
         _scalar_warned = True
 
 
+_events = {}
+
+
 def _wait_current(waiter: torch.device, producer: torch.device) -> None:
-    """Make ``waiter``'s current stream wait for everything queued on ``producer``'s current stream."""
+    """Make ``waiter``'s current stream wait for everything queued on ``producer``'s current stream.
+    One event per (thread, producer, waiter) pair is re-recorded: a wait captures the event's state when it is
+    issued, so re-use is safe and saves an event creation per call (~10 of them per DataParallel step)."""
     if waiter.type != "cuda" or producer.type != "cuda" or waiter == producer:
         return
-    ev = torch.cuda.Event()
+    import threading
+    key = (threading.get_ident(), producer.index, waiter.index)
+    ev = _events.get(key)
+    if ev is None or torch.cuda.is_current_stream_capturing():
+        ev = torch.cuda.Event()
+        if not torch.cuda.is_current_stream_capturing():
+            _events[key] = ev
     ev.record(torch.cuda.current_stream(producer))
     torch.cuda.current_stream(waiter).wait_event(ev)
 
@@ -144,6 +235,9 @@ class Broadcast(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, devices, *params):
+        cache = None
+        if isinstance(devices, tuple) and len(devices) == 2 and isinstance(devices[1], dict):
+            devices, cache = devices                                  # (devices, replica cache of the caller)
         devices = [_dev(d) for d in devices]
         ctx.devices = devices
         ctx.n = len(params)
@@ -151,7 +245,7 @@ class Broadcast(torch.autograd.Function):
         if not params:
             return ()
         outs: List[torch.Tensor] = list(params)                     # replica 0 aliases the originals
-        copies = broadcast_coalesced(params, devices)
+        copies = broadcast_coalesced(params, devices, cache)
         for dev_copies in copies[1:]:
             outs.extend(dev_copies)
         non_diff = [o for o, p in zip(outs[ctx.n:], list(params) * (len(devices) - 1)) if not p.requires_grad]
@@ -167,15 +261,35 @@ class Broadcast(torch.autograd.Function):
         return (None,) + tuple(reduced)
 
 
-def broadcast_coalesced(tensors: Sequence[torch.Tensor], devices: Sequence[torch.device]) -> List[List[torch.Tensor]]:
+def _version_key(tensors: Sequence[torch.Tensor], devices: Sequence[torch.device]):
+    return (tuple(devices), tuple((t.data_ptr(), t._version, t.dtype, tuple(t.shape)) for t in tensors))
+
+
+def broadcast_coalesced(tensors: Sequence[torch.Tensor], devices: Sequence[torch.device],
+                        cache: Optional[dict] = None) -> List[List[torch.Tensor]]:
     """Copy every tensor to every device. Returns ``[per-device list]``; entry 0 is the input list.
 
     CUDA: per dtype the tensors are packed into one flat buffer and pushed to all peers by a single
     store kernel (one read of the source, ``len(devices)-1`` NVLink writes per 16 bytes); the
-    replicas' tensors are views into the destination flats, so there is no unpack pass."""
+    replicas' tensors are views into the destination flats, so there is no unpack pass.
+
+    ``cache`` (a dict owned by the caller, e.g. one per ``DataParallel``): the replicas of the last call are
+    kept together with the (address, version counter) of every source tensor; while nothing was written since
+    -- no ``optimizer.step()``, no in-place buffer update -- the call moves no data and launches nothing (K4:
+    torch's ``replicate`` re-broadcasts on every forward, torch:nn/parallel/replicate.py:108)."""
     devices = [_dev(d) for d in devices]
     out: List[List[Optional[torch.Tensor]]] = [list(tensors)] + [[None] * len(tensors) for _ in devices[1:]]
     if len(devices) == 1 or not tensors:
+        return out
+    if cache is not None:
+        key = _version_key(tensors, devices)
+        if cache.get("key") == key:
+            cache["hits"] = cache.get("hits", 0) + 1
+            return [list(tensors)] + [[c.detach() for c in dev_copies] for dev_copies in cache["copies"][1:]]
+        out = broadcast_coalesced(tensors, devices, None)
+        cache["key"] = key
+        cache["copies"] = [None] + [[c.detach() for c in dev_copies] for dev_copies in out[1:]]
+        cache["misses"] = cache.get("misses", 0) + 1
         return out
     root = tensors[0].device
     if not (_is_cuda(devices) and root.type == "cuda"):
@@ -203,14 +317,18 @@ def broadcast_coalesced(tensors: Sequence[torch.Tensor], devices: Sequence[torch
                 df = torch.empty(total, dtype=dt, device=d)
             _wait_current(root, d)          # d's allocator may still have work queued on that block
             dst_flats.append(df)
-        if len(dst_flats) >= 2 and total >= TWO_LEVEL_MIN_ELEMS:
-            _two_level_broadcast(flat, dst_flats, root)
+        two_level = len(dst_flats) >= 2 and total >= TWO_LEVEL_MIN_ELEMS
+        if two_level:
+            _two_level_broadcast(flat, dst_flats, root)          # (orders the replicas' streams itself)
         else:
             with torch.cuda.device(root):
                 _lib.check(L.b200dt_p2p_broadcast(flat.data_ptr(), _lib.u64_array([f.data_ptr() for f in dst_flats]),
                                                   len(dst_flats), total * esz, _lib.stream_ptr(root)), "p2p_broadcast")
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(root))
         for di, (d, df) in enumerate(zip(devices[1:], dst_flats), start=1):
-            _wait_current(d, root)          # replicas on d start after the push has been issued & done
+            if not two_level:
+                torch.cuda.current_stream(d).wait_event(done)    # replicas on d start after the push is done
             for ti, t, o in zip(idxs, group, offs):
                 out[di][ti] = df[o:o + t.numel()].view(t.shape)
     return out
@@ -233,23 +351,42 @@ def _slices(total: int, parts: int, align: int = 64):
 
 
 def _two_level_broadcast(flat: torch.Tensor, dst_flats: List[torch.Tensor], root: torch.device) -> None:
-    """Scatter + all-gather over NVSwitch: the root sends slice j only to peer j (one payload leaves
-    the root instead of N-1), then the peers exchange slices among themselves in N-2 rounds of
-    disjoint (source, destination) pairs.  Stream-ordered peer copies; no host synchronisation."""
+    """Scatter + all-gather over NVSwitch in N launches: ONE kernel on the root hands slice j to peer j (one
+    payload leaves the root instead of N-1), then ONE kernel per peer pushes its slice to all the other peers
+    (N-2 stores per 16 bytes read).  Ordered with events; no host synchronisation."""
     m = len(dst_flats)
     sl = _slices(flat.numel(), m)
-    with torch.cuda.device(root):
-        for j, df in enumerate(dst_flats):
-            lo, hi = sl[j]
-            if hi > lo:
-                df[lo:hi].copy_(flat[lo:hi], non_blocking=True)
-    for r in range(1, m):                       # round r: peer i hands its slice to peer (i + r) % m
-        for i in range(m):
-            j = (i + r) % m
-            lo, hi = sl[i]
-            if hi > lo:
-                with torch.cuda.device(dst_flats[i].device):
-                    dst_flats[j][lo:hi].copy_(dst_flats[i][lo:hi], non_blocking=True)
+    esz = flat.element_size()
+    L = _lib.lib()
+    srcs = [flat[lo:hi] for (lo, hi) in sl if hi > lo]
+    dsts = [df[lo:hi] for df, (lo, hi) in zip(dst_flats, sl) if hi > lo]
+    _multi_copy(srcs, dsts, root)
+    # one event per producer, any number of waiters.  The peers' destination blocks need no wait of their own:
+    # the root waited for every peer's allocator state before the hand-out, and each push waits for the root.
+    handed = torch.cuda.Event()
+    handed.record(torch.cuda.current_stream(root))
+    pushed = {}
+    for i, df in enumerate(dst_flats):
+        lo, hi = sl[i]
+        if hi <= lo:
+            continue
+        d = df.device
+        torch.cuda.current_stream(d).wait_event(handed)          # slice i has arrived on peer i
+        others = [o for j, o in enumerate(dst_flats) if j != i]
+        with torch.cuda.device(d):
+            _lib.check(L.b200dt_p2p_broadcast(df.data_ptr() + lo * esz,
+                                              _lib.u64_array([o.data_ptr() + lo * esz for o in others]), len(others),
+                                              (hi - lo) * esz, _lib.stream_ptr(d)), "p2p_broadcast")
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(d))
+        pushed[i] = ev
+    for j, df in enumerate(dst_flats):          # replica j runs after every slice has been pushed into it
+        sj = torch.cuda.current_stream(df.device)
+        for i, ev in pushed.items():
+            if i != j:
+                sj.wait_event(ev)
+        if j not in pushed:
+            sj.wait_event(handed)
 
 
 def _two_level_reduce(flats: List[torch.Tensor], devs: List[torch.device], root: torch.device) -> torch.Tensor:

@@ -10,7 +10,13 @@ B200-first differences from ``torch.nn.DataParallel``: parameters travel as one 
 NVLink peer stores and replica parameters are views into the received buffer; gradients come back
 through one pull-reduce kernel; worker threads pin their CUDA device *before* the first library
 call (the reference's run shows what happens otherwise: the cuBLAS "no current CUDA context"
-warning at 01.data_parallel.ipynb:315); ``forward_sum`` fuses the output gather with a sum loss.
+warning at 01.data_parallel.ipynb:315); ``forward_sum`` fuses the output gather with a sum loss; the
+replicas' parameters are re-broadcast only after something wrote the originals (version counters).
+
+Credit: the container recursion of ``scatter`` / ``gather`` below (tensor / namedtuple / tuple / list / dict /
+other, in that order, and the "All dicts must have the same number of keys" check) follows PyTorch's
+``torch/nn/parallel/scatter_gather.py`` (BSD-3-Clause, (c) the PyTorch contributors) closely on purpose: these
+semantics are the API contract ``nn.DataParallel`` users rely on, and the CPU tests compare against it case by case.
 """
 from __future__ import annotations
 
@@ -74,7 +80,8 @@ def gather(outputs: Sequence, target_device, dim: int = 0):
     return gather_map(list(outputs))
 
 
-def replicate(module: nn.Module, devices: Sequence, detach: bool = False) -> List[nn.Module]:
+def replicate(module: nn.Module, devices: Sequence, detach: bool = False,
+              cache: Optional[dict] = None) -> List[nn.Module]:
     """Functional copies of ``module`` on each device. Replica 0 shares storage with the original
     (in-place buffer updates such as BatchNorm statistics survive); the other replicas hold
     non-leaf parameter tensors produced by ``Broadcast`` so gradients flow back to the originals."""
@@ -82,12 +89,14 @@ def replicate(module: nn.Module, devices: Sequence, detach: bool = False) -> Lis
     n = len(devices)
     params = list(module.parameters())
     p_index = {p: i for i, p in enumerate(params)}
+    pcache = cache.setdefault("params", {}) if cache is not None else None
+    bcache = cache.setdefault("buffers", {}) if cache is not None else None
     if params:
         if detach:
-            per_dev = comm.broadcast_coalesced([p.detach() for p in params], devices)
-            per_dev[0] = [p.detach() for p in params]
+            per_dev = comm.broadcast_coalesced(params, devices, pcache)
+            per_dev = [[t.detach() for t in lst] for lst in per_dev]
         else:
-            flat = Broadcast.apply(devices, *params)
+            flat = Broadcast.apply((devices, pcache) if pcache is not None else devices, *params)
             per_dev = [list(flat[i * len(params):(i + 1) * len(params)]) for i in range(n)]
     else:
         per_dev = [[] for _ in range(n)]
@@ -95,7 +104,7 @@ def replicate(module: nn.Module, devices: Sequence, detach: bool = False) -> Lis
     b_index = {b: i for i, b in enumerate(buffers)}
     if buffers:
         with torch.no_grad():
-            b_per_dev = comm.broadcast_coalesced([b.detach() for b in buffers], devices)
+            b_per_dev = comm.broadcast_coalesced(buffers, devices, bcache)
         b_per_dev[0] = list(buffers)
     else:
         b_per_dev = [[] for _ in range(n)]
@@ -206,6 +215,9 @@ class DataParallel(nn.Module):
                  threaded: Optional[bool] = None) -> None:
         super().__init__()
         self.threaded = threaded
+        # replicas of the parameters / buffers survive between forwards until a source tensor is written
+        # (version counters): no re-broadcast for evaluation loops or several forwards per optimizer step
+        self._replica_cache: dict = {}
         if device_ids is None:
             device_ids = list(range(torch.cuda.device_count())) if torch.cuda.is_available() else []
         self.module = module
@@ -232,7 +244,7 @@ class DataParallel(nn.Module):
         if len(self.device_ids) == 1:
             return [self.module(*s_in[0], **s_kw[0])]
         used = self.device_ids[:len(s_in)]
-        replicas = replicate(self.module, used, detach=not torch.is_grad_enabled())
+        replicas = replicate(self.module, used, detach=not torch.is_grad_enabled(), cache=self._replica_cache)
         threaded = self.threaded if self.threaded is not None else any(d.type != "cuda" for d in used)
         return parallel_apply(replicas, s_in, s_kw, used, threaded=threaded)
 

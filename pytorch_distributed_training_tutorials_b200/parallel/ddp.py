@@ -230,7 +230,7 @@ class DistributedDataParallel(nn.Module):
                 tb16 = self._params[ids[0]].dtype == torch.bfloat16
                 b.table = coll.TensorTable([self._params[j].numel() for j in ids], self.device,
                                            self.comm_dtype == "bf16", tb16, target_blocks=self.max_comm_blocks)
-                b.mode = coll.pick_mode(b.table.stage_bytes, self._arena, self.allreduce)
+                b.mode = coll.pick_mode(b.table.stage_bytes, self._arena, self.allreduce, b.table.wire_bf16)
             out.append(b)
         self._assign_grad_views(out)
         return out

@@ -207,3 +207,48 @@ def test_graphed_data_parallel_matches_single_device_training():
             assert pd.device.index == d
     with pytest.raises(ValueError):
         gdp.train_step(xb[:8], yb[:8])
+
+
+@needs2
+def test_data_parallel_replica_cache_and_kernel_scatter_gather():
+    """Parameters are re-broadcast only after something wrote them (version counters); scatter and gather are one
+    kernel each and agree with torch's DataParallel, for even and ragged batches."""
+    import pytorch_distributed_training_tutorials_b200 as b2
+    from pytorch_distributed_training_tutorials_b200.models.toy import MLP
+    n = min(_ngpu(), 8)
+    torch.manual_seed(0)
+    m = MLP(64, 128, 2, 16).to("cuda:0")
+    ref = copy.deepcopy(m)
+    dp = b2.DataParallel(m, device_ids=list(range(n)))
+    rdp = torch.nn.DataParallel(ref, device_ids=list(range(n)))
+    opt = b2.FusedSGD(m.parameters(), lr=0.05, bf16_shadow=False)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    for B in (8 * n, 8 * n + 3, n - 1 if n > 2 else 3):
+        x = torch.randn(B, 64, device="cuda:0")
+        with torch.no_grad():
+            a = dp(x); b = dp(x)                     # second forward: nothing was written -> no broadcast
+        assert torch.equal(a, b)
+        c = rdp(x)
+        assert a.shape == c.shape and torch.allclose(a.float(), c.float(), atol=3e-2, rtol=3e-2)
+    pc = dp._replica_cache["params"]
+    assert pc["hits"] >= 3 and pc["misses"] >= 1
+    misses = pc["misses"]
+    x = torch.randn(8 * n, 64, device="cuda:0"); y = torch.randn(8 * n, 16, device="cuda:0")
+    for it in range(3):
+        opt.zero_grad(); torch.nn.functional.mse_loss(dp(x).float(), y).backward(); opt.step()
+        ropt.zero_grad(); torch.nn.functional.mse_loss(rdp(x), y).backward(); ropt.step()
+    assert pc["misses"] == misses + 3                # every optimizer step invalidated the replicas
+    for p, q in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, atol=2e-2, rtol=2e-2)
+    # gather of scalars (one per replica) and the gradient scatter behind it
+    class S(torch.nn.Module):
+        def __init__(self):
+            super().__init__(); self.w = torch.nn.Parameter(torch.ones(4))
+        def forward(self, x):
+            return (x * self.w).sum()
+    sm = S().to("cuda:0"); sdp = b2.DataParallel(sm, device_ids=list(range(n)))
+    xs = torch.randn(4 * n, 4, device="cuda:0")
+    out = sdp(xs)
+    assert out.shape == (n,)
+    out.sum().backward()
+    assert torch.allclose(sm.w.grad, xs.sum(0), atol=1e-4)

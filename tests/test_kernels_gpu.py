@@ -327,3 +327,63 @@ def test_layout_helpers():
     assert torch.equal(NV.transpose_bf16(a), a.t().contiguous())
     w = torch.randn(1001, device=dev())
     assert torch.equal(NV.cast_bf16(w), w.bfloat16())
+
+
+def test_multi_copy_kernel_segments():
+    """DataParallel's scatter / gather kernel: up to eight (src, dst, bytes) segments in one launch, 16-byte
+    vector path and byte path (odd sizes / odd addresses)."""
+    import ctypes
+    from pytorch_distributed_training_tutorials_b200 import _lib
+    dev = torch.device("cuda:0")
+    for sizes, skew in (([4096, 16, 1 << 20, 48], 0), ([3, 1001, 17], 0), ([4096, 4096], 4), ([1 << 22], 0)):
+        srcs = [torch.randint(0, 255, (n + skew,), dtype=torch.uint8, device=dev)[skew:] for n in sizes]
+        dsts = [torch.zeros(n + 32, dtype=torch.uint8, device=dev) for n in sizes]
+        nb = (ctypes.c_longlong * len(sizes))(*sizes)
+        _lib.check(_lib.lib().b200dt_p2p_multi_copy(_lib.u64_array([t.data_ptr() for t in srcs]),
+                                                    _lib.u64_array([t.data_ptr() for t in dsts]), nb, len(sizes),
+                                                    _lib.stream_ptr(dev)), "multi_copy")
+        torch.cuda.synchronize()
+        for s_, d_, n in zip(srcs, dsts, sizes):
+            assert torch.equal(d_[:n], s_) and int(d_[n:].sum()) == 0
+
+
+def test_fused_adam_capturable_matches_torch_and_replays_from_a_graph():
+    """Adam with the step count on the device (the reference trains its DataParallel model with Adam,
+    01.data_parallel.ipynb:287): eager steps match torch.optim.Adam, and the captured step keeps matching when
+    it is replayed -- the bias corrections follow the device-side count, not a value frozen at capture."""
+    from pytorch_distributed_training_tutorials_b200.ops.optim import FusedAdam
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    shapes = [(257, 33), (1000,), (64, 64), (5,)]
+    ps = [torch.randn(s, device=dev, requires_grad=True) for s in shapes]
+    qs = [p.detach().clone().requires_grad_(True) for p in ps]
+    mine = FusedAdam(ps, lr=1e-2, capturable=True, bf16_shadow=False)
+    ref = torch.optim.Adam(qs, lr=1e-2)
+    grads = [[torch.randn(s, device=dev) for s in shapes] for _ in range(7)]
+
+    def set_grads(k):
+        for p, q, g in zip(ps, qs, grads[k]):
+            if p.grad is None:
+                p.grad = g.clone(); q.grad = g.clone()
+            else:
+                p.grad.copy_(g); q.grad.copy_(g)
+    for k in range(3):
+        set_grads(k)
+        mine.step(); ref.step()
+    for p, q in zip(ps, qs):
+        assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)
+    assert float(mine.state[ps[0]]["step"]) == 3.0
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            mine.step()
+    torch.cuda.current_stream().wait_stream(s)
+    for k in range(3, 7):
+        set_grads(k)
+        g.replay(); ref.step()
+    torch.cuda.synchronize()
+    assert float(mine.state[ps[0]]["step"]) == 7.0
+    for p, q in zip(ps, qs):
+        assert torch.allclose(p, q, rtol=2e-5, atol=2e-6), float((p - q).abs().max())
