@@ -27,7 +27,9 @@ constexpr int kBK = 64;           // K elements per stage (one 128-byte swizzle 
 constexpr int kThreads = 320;          // 2 control warps + 8 epilogue warps
 constexpr int kMaxTaps = 9;
 constexpr int kMaxMaps = 4;
-constexpr int kColAccBytes = 2 * 256 * 4;      // fused BN statistics: {sum, sumsq}[256] of the current tile
+constexpr int kColAccBytes = 4 * 2 * 256 * 4;  // fused BN statistics: {sum, sumsq}[256] of the current tile, one copy
+                                               // per TMEM lane quarter (plain stores, no shared atomics); only
+                                               // reserved when the launch asks for statistics
 constexpr int kStageOutBytes = 128 * 128;   // 8 epilogue warps x (32 rows x 128 B); x2 = budget kept for staging
 
 struct Tap {
@@ -59,6 +61,7 @@ struct GemmParams {
   int bn_C;                 // channels of that BN (== n_valid)
   int b_mn;                 // kind 0 only: B operand is MN-major (dgrad reads the filter un-transposed)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
+  int colacc_bytes;         // kColAccBytes when bn_sums != nullptr, else 0
   const float* bias;
   // deterministic mode (b200::deterministic()): sums are combined in a fixed order
   int det;                  // 1: no floating-point atomics anywhere in this launch
@@ -134,8 +137,8 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   const int b_stage_bytes = p.BN * kBK * 2;           // 8..32 KB
   const int stage_bytes = a_stage_bytes + b_stage_bytes;
   uint8_t* stage_out = smem + p.stages * stage_bytes;          // 2 x 16 KB epilogue staging
-  float* col_acc = reinterpret_cast<float*>(stage_out + 2 * kStageOutBytes);     // [2][256]
-  Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes + kColAccBytes);
+  float* col_acc = reinterpret_cast<float*>(stage_out + 2 * kStageOutBytes);     // [4 quarters][2][256]
+  Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes + p.colacc_bytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -158,8 +161,6 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   if (warp == 1) {
     tmem_alloc<512>(&bars->tmem_base);
   }
-  if (p.bn_sums != nullptr)
-    for (int i = threadIdx.x; i < kColAccBytes / 4; i += blockDim.x) col_acc[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -430,22 +431,11 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
               const float2 f = unpack_bf16x2(u);
               s0 += f.x; s1 += f.y; q0 += f.x * f.x; q1 += f.y * f.y;
             }
-            float* accb = col_acc;
+            // every (quarter, column) pair has exactly one writer per tile: plain stores, fixed order later
+            float* accb = col_acc + q * 512;
             const int cc = sl * 64 + lane * 2;
-            if (!p.det) {
-              atomicAdd(accb + cc, s0); atomicAdd(accb + cc + 1, s1);
-              atomicAdd(accb + 256 + cc, q0); atomicAdd(accb + 256 + cc + 1, q1);
-            } else {
-              // fixed order: the four quarter-warps that share this slab (same pi) add in turn
-#pragma unroll 1
-              for (int turn = 0; turn < 4; ++turn) {
-                if (turn == q) {
-                  accb[cc] += s0; accb[cc + 1] += s1;
-                  accb[256 + cc] += q0; accb[256 + cc + 1] += q1;
-                }
-                if (turn < 3) asm volatile("bar.sync %0, 128;" ::"r"(3 + pi) : "memory");
-              }
-            }
+            *reinterpret_cast<float2*>(accb + cc) = make_float2(s0, s1);
+            *reinterpret_cast<float2*>(accb + 256 + cc) = make_float2(q0, q1);
           }
           if (lane == 0) {
             if (p.atomic)
@@ -512,14 +502,15 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         const int e = (warp - 2) * 32 + lane;          // 0..255: one column per thread
         if (e < p.BN) {
           const int c = col_base + e;
-          const float sv = accb[e], qv = accb[256 + e];
-          accb[e] = 0.f; accb[256 + e] = 0.f;
           if (c < p.n_valid) {
+            // quarters in a fixed order: the tile's column sums do not depend on warp timing
+            const float sv = ((accb[e] + accb[512 + e]) + accb[1024 + e]) + accb[1536 + e];
+            const float qv = ((accb[256 + e] + accb[768 + e]) + accb[1280 + e]) + accb[1792 + e];
             if (p.det) { dstb[c] += sv; dstb[p.bn_C + c] += qv; }
             else { atomicAdd(dstb + c, sv); atomicAdd(dstb + p.bn_C + c, qv); }
           }
         }
-        asm volatile("bar.sync 2, 256;" ::: "memory");      // cleared before the next tile adds
+        asm volatile("bar.sync 2, 256;" ::: "memory");      // all read before the next tile overwrites
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -656,7 +647,8 @@ static int num_sms() {
 static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
                   const CUtensorMap* mapC, GemmParams& p, cudaStream_t stream) {
   const int stage_bytes = kBM * kBK * 2 + p.BN * kBK * 2;
-  const int fixed = 2 * kStageOutBytes + kColAccBytes + (int)sizeof(Barriers) + 64;
+  p.colacc_bytes = p.bn_sums != nullptr ? kColAccBytes : 0;
+  const int fixed = 2 * kStageOutBytes + p.colacc_bytes + (int)sizeof(Barriers) + 64;
   int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return -2;

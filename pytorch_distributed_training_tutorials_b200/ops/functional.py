@@ -68,7 +68,18 @@ class _Linear(torch.autograd.Function):
         dy2 = dy.reshape(-1, N)
         dx = dw = db = None
         want_db = ctx.has_bias and ctx.needs_input_grad[2]
-        if N % 8 == 0 and (ctx.relu or want_db) and (not ctx.relu or y.dtype == BF16):
+        if N % 8:
+            # an output width the TMA row pitch cannot take (e.g. a 1001-way head): the backward runs on the
+            # fp32 SIMT kernels of csrc/skinny.cu -- still this library's code, no cuBLAS call
+            if ctx.relu:
+                dy2 = dy2 * (y > 0)
+            dyf = dy2.contiguous() if dy2.dtype == F32 else NV.cast_f32(dy2.contiguous())
+            dx, dw, db = NV.skinny_linear_bwd(dyf, NV.cast_f32(x2), weight.detach().contiguous(),
+                                              ctx.needs_input_grad[0], ctx.needs_input_grad[1], want_db)
+            if dx is not None:
+                dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
+            return dx, dw, db, None, None
+        if (ctx.relu or want_db) and (not ctx.relu or y.dtype == BF16):
             # ReLU mask and bias gradient in one pass (bf16 in, bf16 out, fp32 column sums)
             dyb, db = NV.relu_bwd_bias(dy2.to(BF16).contiguous(), y.reshape(-1, N) if ctx.relu else None, want_db)
             dy2 = dyb
@@ -78,16 +89,10 @@ class _Linear(torch.autograd.Function):
                 dy2 = dy2 * (y > 0)
             dyb = dy2.to(BF16).contiguous()
         if ctx.needs_input_grad[0]:
-            if N % 8 == 0:
-                # W [out, in] is consumed in place as the MN-major B operand: no transposed copy
-                dx = NV.gemm_nn(dyb, _shadow(weight)).view(ctx.x_shape).to(ctx.x_dtype)
-            else:
-                dx = (dy2.float() @ weight.detach()).view(ctx.x_shape).to(ctx.x_dtype)
+            # W [out, in] is consumed in place as the MN-major B operand: no transposed copy
+            dx = NV.gemm_nn(dyb, _shadow(weight)).view(ctx.x_shape).to(ctx.x_dtype)
         if ctx.needs_input_grad[1]:
-            if N % 8 == 0 and Kf % 8 == 0:
-                dw = NV.gemm_nt_reduce(dyb, x2, out=_grad_out(weight))
-            else:
-                dw = dy2.float().t() @ x2.float()
+            dw = NV.gemm_nt_reduce(dyb, x2, out=_grad_out(weight))
         if want_db:
             db = dy2.float().sum(0)
         return dx, dw, db, None, None
@@ -248,6 +253,21 @@ def conv2d_dual(x, w1, w2, stride1: int = 1, stride2: int = 1):
     return _ConvDual.apply(x, w1, w2, stride1, stride2)
 
 
+def _stem_operand(w: torch.Tensor) -> torch.Tensor:
+    """The stem filter as the GEMM's B operand: bf16 ``[Cout, 160]`` (K = 147 zero-padded to the TMA row pitch),
+    cached until the fp32 master changes -- it used to be rebuilt with a fill and a strided copy every forward."""
+    cache = getattr(w, "_b200_stem_operand", None)
+    if cache is not None and cache[0] == w._version and cache[1].device == w.device:
+        return cache[1]
+    wk = torch.zeros((w.shape[0], NV.STEM_LDK), device=w.device, dtype=BF16)
+    wk[:, :147] = w.detach().reshape(w.shape[0], 147)
+    try:
+        w._b200_stem_operand = (w._version, wk)
+    except Exception:  # pragma: no cover
+        pass
+    return wk
+
+
 class _StemConv(torch.autograd.Function):
     """7x7 stride-2 pad-3 convolution of the fp32 NCHW network input (Cin = 3)."""
 
@@ -255,8 +275,7 @@ class _StemConv(torch.autograd.Function):
     def forward(ctx, x, weight, with_stats):
         NB, _, H, W = x.shape
         cols = NV.stem_im2col(x.contiguous())
-        wk = torch.zeros((weight.shape[0], NV.STEM_LDK), device=x.device, dtype=BF16)
-        wk[:, :147] = weight.detach().reshape(weight.shape[0], 147)
+        wk = _stem_operand(weight)
         sums = NV.bn_sums_buffer(weight.shape[0], x.device) if with_stats else None
         ctx.set_materialize_grads(False)
         y = NV.gemm_tn(cols, wk, bn_sums=sums)

@@ -209,6 +209,17 @@ def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     return out
 
 
+def cast_f32(src: torch.Tensor) -> torch.Tensor:
+    """bf16 (or fp32) -> fp32 copy on the library's own cast kernel (no ATen elementwise launch)."""
+    if src.dtype == F32:
+        return src
+    _need(src, BF16, "src")
+    out = torch.empty(src.shape, device=src.device, dtype=F32)
+    with on_device(src.device):
+        check(lib().b200dt_cast_to_f32(ptr(src), ptr(out), src.numel(), 1, stream_ptr(src.device)), "cast_f32")
+    return out
+
+
 def transpose_bf16(src: torch.Tensor) -> torch.Tensor:
     _need(src, BF16, "src")
     r, c = src.shape

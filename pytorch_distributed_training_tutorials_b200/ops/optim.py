@@ -177,6 +177,14 @@ class FusedAdam(_FusedBase):
         self.capturable = capturable
         self._step_state: Dict[tuple, torch.Tensor] = {}
 
+    def load_state_dict(self, state_dict) -> None:
+        super().load_state_dict(state_dict)
+        # the device-side step counters follow the loaded per-parameter counts
+        for (gi, dev), ss in self._step_state.items():
+            vals = [float(self.state[p]["step"]) for p in self.param_groups[gi]["params"]
+                    if p.device == dev and "step" in self.state.get(p, {})]
+            ss[0] = max(vals) if vals else 0.0
+
     def _step_capturable(self, grad_scale: float):
         for gi, group in enumerate(self.param_groups):
             b1, b2 = group["betas"]

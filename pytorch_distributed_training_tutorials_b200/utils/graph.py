@@ -8,7 +8,8 @@ eager PyTorch only; this is the B200-side replacement for a tracing compiler: st
 
 Works with: the sm_100a ops of this package, ``FusedSGD``, ``DistributedDataParallel`` (the bucket
 kernels run on the side stream inside the captured region; every rank must capture and replay in
-lock-step).  Not capturable: ``FusedAdam`` (host-side step count), data-dependent Python control flow.
+lock-step), ``FusedAdam(capturable=True)`` (device-side step count).  Not capturable: data-dependent
+Python control flow, optimizers that keep their step count on the host.
 """
 from __future__ import annotations
 
@@ -50,10 +51,19 @@ class GraphedTrainStep:
         torch.cuda.synchronize(self.device)
         self.graph = torch.cuda.CUDAGraph()
         self.optimizer.zero_grad(set_to_none=True)
-        before = _lib.launch_count
+        before = _lib.launch_count + self._reducer_launches()
         with torch.cuda.graph(self.graph):
             self.static_loss = self._eager(zero=False)
-        self.kernels_per_step = _lib.launch_count - before
+        self.kernels_per_step = _lib.launch_count + self._reducer_launches() - before
+
+    def _reducer_launches(self) -> int:
+        """Collectives the C++ reducer launched itself (they never pass through the ctypes counter)."""
+        n = 0
+        for m in self.model.modules():
+            r = getattr(m, "_reducer", None)
+            if r is not None and hasattr(r, "stats"):
+                n += int(r.stats().get("native_launches", 0))
+        return n
 
     def _snapshot(self):
         import copy

@@ -387,3 +387,22 @@ def test_fused_adam_capturable_matches_torch_and_replays_from_a_graph():
     assert float(mine.state[ps[0]]["step"]) == 7.0
     for p, q in zip(ps, qs):
         assert torch.allclose(p, q, rtol=2e-5, atol=2e-6), float((p - q).abs().max())
+
+
+def test_linear_with_an_output_width_that_is_not_a_multiple_of_8():
+    """A 1001-way head: forward on tcgen05, backward on the SIMT kernels -- no cuBLAS fallback."""
+    from pytorch_distributed_training_tutorials_b200.ops import nn as bnn
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    lin = bnn.Linear(2048, 1001).to(dev)
+    assert not lin.skinny
+    ref = torch.nn.Linear(2048, 1001).to(dev)
+    ref.load_state_dict(lin.state_dict())
+    x = torch.randn(96, 2048, device=dev)
+    xr = x.clone().requires_grad_(True); x.requires_grad_(True)
+    t = torch.randn(96, 1001, device=dev)
+    y = lin(x); yr = ref(xr)
+    assert torch.allclose(y, yr, rtol=2e-2, atol=2e-2)
+    (y * t).sum().backward(); (yr * t).sum().backward()
+    for a, b in ((x.grad, xr.grad), (lin.weight.grad, ref.weight.grad), (lin.bias.grad, ref.bias.grad)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-2
