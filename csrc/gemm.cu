@@ -62,6 +62,13 @@ struct GemmParams {
   int b_mn;                 // kind 0 only: B operand is MN-major (dgrad reads the filter un-transposed)
   int tma_store;            // epilogue stages tiles in smem and stores them with TMA (mapC)
   int colacc_bytes;         // kColAccBytes when bn_sums != nullptr, else 0
+  // Tile index as mixed-radix digits (no integer division per tile in any warp role: a tile of a short-K
+  // convolution lasts ~1.5 us and the single producer thread used to spend a third of that dividing).
+  //   kind 0: (n_blk | tw | th | tn) with radices (tiles_n, tiles_w, tiles_h, -);
+  //   kind 1: (n_blk | m_blk | split | 0) with radices (tiles_n, tiles_m, -, -).
+  // step[] are the digits of gridDim.x, i.e. what one iteration of the persistent loop adds.
+  int rad[3];
+  int step[4];
   const float* bias;
   // deterministic mode (b200::deterministic()): sums are combined in a fixed order
   int det;                  // 1: no floating-point atomics anywhere in this launch
@@ -83,6 +90,26 @@ struct alignas(8) Barriers {
   uint32_t tmem_base;
   uint32_t pad;
 };
+
+struct TileCoord { int d0, d1, d2, d3; };
+__device__ __forceinline__ void tile_init(const GemmParams& p, int t, TileCoord& c) {
+  c.d0 = t % p.rad[0]; t /= p.rad[0];
+  c.d1 = t % p.rad[1]; t /= p.rad[1];
+  c.d2 = t % p.rad[2];
+  c.d3 = t / p.rad[2];
+}
+__device__ __forceinline__ void tile_next(const GemmParams& p, TileCoord& c) {
+  c.d0 += p.step[0];
+  int k = c.d0 >= p.rad[0] ? 1 : 0;
+  c.d0 -= k ? p.rad[0] : 0;
+  c.d1 += p.step[1] + k;
+  k = c.d1 >= p.rad[1] ? 1 : 0;
+  c.d1 -= k ? p.rad[1] : 0;
+  c.d2 += p.step[2] + k;
+  k = c.d2 >= p.rad[2] ? 1 : 0;
+  c.d2 -= k ? p.rad[2] : 0;
+  c.d3 += p.step[3] + k;
+}
 
 __device__ __forceinline__ void store_chunk(const GemmParams& p, const float (&f)[32],
                                             long long row_off, int col0, bool row_ok) {
@@ -176,16 +203,16 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       const uint32_t full0 = smem_u32(&bars->full[0]);
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int n_blk = t % p.tiles_n;
-        const int m_blk = (t / p.tiles_n) % p.tiles_m;
-        const int split = t / (p.tiles_n * p.tiles_m);
+      TileCoord tc;
+      tile_init(p, blockIdx.x, tc);
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
+        const int n_blk = tc.d0;
+        const int m_blk = tc.d1;                          // kind 1 only
+        const int split = p.kind == 1 ? tc.d2 : 0;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
         if (p.kind == 0) {
-          const int tw = m_blk % p.tiles_w;
-          const int th = (m_blk / p.tiles_w) % p.tiles_h;
-          const int tn = m_blk / (p.tiles_w * p.tiles_h);
+          const int tw = tc.d1, th = tc.d2, tn = tc.d3;
           const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
           const int nb0 = n_blk * p.BN;
           int kcoord = 0;
@@ -274,8 +301,10 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int split = t / (p.tiles_n * p.tiles_m);
+      TileCoord tc;
+      tile_init(p, blockIdx.x, tc);
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
+        const int split = p.kind == 1 ? tc.d2 : 0;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
         mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
@@ -311,17 +340,15 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
     uint8_t* buf = stage_out + (warp - 2) * 4096;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int n_blk = t % p.tiles_n;
-      const int m_blk = (t / p.tiles_n) % p.tiles_m;
-      const int split = t / (p.tiles_n * p.tiles_m);
+    TileCoord tc;
+    tile_init(p, blockIdx.x, tc);
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
+      const int n_blk = tc.d0;
+      const int m_blk = tc.d1;              // kind 1 only
+      const int split = p.kind == 1 ? tc.d2 : 0;
       const int col_base = n_blk * p.BN;   // WGRAD: taps are consecutive, tap * Cin + ct * BN
       int tw = 0, th = 0, tn = 0;
-      if (p.kind == 0) {
-        tw = m_blk % p.tiles_w;
-        th = (m_blk / p.tiles_w) % p.tiles_h;
-        tn = m_blk / (p.tiles_w * p.tiles_h);
-      }
+      if (p.kind == 0) { tw = tc.d1; th = tc.d2; tn = tc.d3; }
       mbar_wait(&bars->tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * p.BN;
@@ -420,22 +447,45 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
           fence_proxy_async();             // generic-proxy smem writes -> visible to TMA
           __syncwarp();
           if (p.bn_sums != nullptr && !p.out_fp32) {
-            // Fused BatchNorm statistics: lane l owns columns 2l, 2l+1 of this 64-column slab and
-            // adds up this warp's 32 rows straight from the staged (already bf16-rounded) tile;
-            // rows outside the tensor hold exact zeros (TMA zero fill), so they do not count.
-            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-            const uint8_t* colp = buf + ((lane & 3) << 2);
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r) {
-              const uint32_t u = *reinterpret_cast<const uint32_t*>(colp + r * 128 + (((lane >> 2) ^ (r & 7)) << 4));
-              const float2 f = unpack_bf16x2(u);
-              s0 += f.x; s1 += f.y; q0 += f.x * f.x; q1 += f.y * f.y;
+            // Fused BatchNorm statistics of this warp's 32 rows x 64 columns, straight from the staged (already
+            // bf16-rounded) tile; rows outside the tensor hold exact zeros (TMA zero fill), so they do not
+            // count.  Lane l reads the 16-byte chunk (l & 7) = 8 columns of rows (l >> 3) * 8 .. + 7 with
+            // LDS.128 (conflict-free under the 128-byte swizzle) and accumulates with packed fp32x2 math;
+            // the four row groups are then combined with two shuffle rounds.
+            const int c8 = lane & 7, rg = lane >> 3;
+            float2 sm2[4], sq2[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { sm2[k] = make_float2(0.f, 0.f); sq2[k] = make_float2(0.f, 0.f); }
+            const uint8_t* rowp = buf + rg * (8 * 128);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint4 u = *reinterpret_cast<const uint4*>(rowp + i * 128 + ((c8 ^ i) << 4));
+              const uint32_t wv[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float2 f = make_float2(__uint_as_float(wv[k] << 16), __uint_as_float(wv[k] & 0xffff0000u));
+                sm2[k] = __fadd2_rn(sm2[k], f);
+                sq2[k] = __ffma2_rn(f, f, sq2[k]);
+              }
             }
-            // every (quarter, column) pair has exactly one writer per tile: plain stores, fixed order later
-            float* accb = col_acc + q * 512;
-            const int cc = sl * 64 + lane * 2;
-            *reinterpret_cast<float2*>(accb + cc) = make_float2(s0, s1);
-            *reinterpret_cast<float2*>(accb + 256 + cc) = make_float2(q0, q1);
+#pragma unroll
+            for (int off = 8; off <= 16; off <<= 1) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                sm2[k].x += __shfl_xor_sync(0xffffffffu, sm2[k].x, off);
+                sm2[k].y += __shfl_xor_sync(0xffffffffu, sm2[k].y, off);
+                sq2[k].x += __shfl_xor_sync(0xffffffffu, sq2[k].x, off);
+                sq2[k].y += __shfl_xor_sync(0xffffffffu, sq2[k].y, off);
+              }
+            }
+            if (rg == 0) {
+              // every (quarter, column) pair has exactly one writer per tile: plain stores, fixed order later
+              float* accb = col_acc + q * 512 + sl * 64 + c8 * 8;
+              *reinterpret_cast<float4*>(accb) = make_float4(sm2[0].x, sm2[0].y, sm2[1].x, sm2[1].y);
+              *reinterpret_cast<float4*>(accb + 4) = make_float4(sm2[2].x, sm2[2].y, sm2[3].x, sm2[3].y);
+              *reinterpret_cast<float4*>(accb + 256) = make_float4(sq2[0].x, sq2[0].y, sq2[1].x, sq2[1].y);
+              *reinterpret_cast<float4*>(accb + 260) = make_float4(sq2[2].x, sq2[2].y, sq2[3].x, sq2[3].y);
+            }
           }
           if (lane == 0) {
             if (p.atomic)
@@ -672,6 +722,16 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   int grid = total < num_sms() ? total : num_sms();
   if (p.det && p.bn_sums != nullptr && grid > p.bn_reps) grid = p.bn_reps;   // one statistics slot per CTA
   if (grid <= 0) return 0;
+  p.rad[0] = p.tiles_n;
+  p.rad[1] = p.kind == 0 ? p.tiles_w : p.tiles_m;
+  p.rad[2] = p.kind == 0 ? p.tiles_h : (1 << 30);
+  {
+    int g = grid;
+    p.step[0] = g % p.rad[0]; g /= p.rad[0];
+    p.step[1] = g % p.rad[1]; g /= p.rad[1];
+    p.step[2] = g % p.rad[2];
+    p.step[3] = g / p.rad[2];
+  }
   TmaMaps maps;
   for (int i = 0; i < kMaxMaps; ++i) { maps.a[i] = mapsA[i]; maps.b[i] = mapsB[i]; }
   maps.c = mapC != nullptr ? *mapC : mapsA[0];
