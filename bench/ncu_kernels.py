@@ -81,6 +81,28 @@ def family(name):
     if name == "stem":
         x = torch.randn(NB, 3, 224, 224, device=dev)
         return (lambda: NV.stem_im2col(x)), x.numel() * 4 + NB * 112 * 112 * 160 * 2, 0
+    if name in ("stem_implicit", "stem_implicit_fwd", "stem_implicit_wgrad"):
+        x = torch.randn(NB, 3, 224, 224, device=dev); w = torch.randn(64, 7, 7, 3, device=dev) * 0.1
+        sums = NV.bn_sums_buffer(64, dev)
+        dy = torch.randn(NB, 112, 112, 64, device=dev).to(bf)
+        fl = 2.0 * NB * 112 * 112 * 64 * 147
+        if name == "stem_implicit_fwd":
+            return (lambda: NV.stem_conv_fprop(x, w, bn_sums=sums)), x.numel() * 4 + dy.numel() * 2, fl
+        if name == "stem_implicit_wgrad":
+            return (lambda: NV.stem_conv_wgrad(x, dy)), x.numel() * 4 + dy.numel() * 2, fl
+        return (lambda: (NV.stem_conv_fprop(x, w, bn_sums=sums), NV.stem_conv_wgrad(x, dy))), \
+            2 * x.numel() * 4 + 2 * dy.numel() * 2, 2 * fl
+    if name == "stem_explicit":
+        x = torch.randn(NB, 3, 224, 224, device=dev)
+        wk = torch.randn(64, 160, device=dev).to(bf)
+        sums = NV.bn_sums_buffer(64, dev)
+        dy = torch.randn(NB * 112 * 112, 64, device=dev).to(bf)
+
+        def run():
+            cols = NV.stem_im2col(x)
+            NV.gemm_tn(cols, wk, bn_sums=sums)
+            NV.gemm_nt_reduce(dy, cols)
+        return run, 3 * NB * 112 * 112 * 160 * 2 + x.numel() * 4 + 2 * dy.numel() * 2, 2 * 2.0 * NB * 112 * 112 * 64 * 160
     if name == "sgd":
         from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD
         ps = [torch.randn(2048, 1024, device=dev, requires_grad=True) for _ in range(12)]
@@ -116,7 +138,7 @@ def family(name):
 FAMILIES = ["conv_fprop_56_64_256_1_1", "conv_fprop_56_64_64_3_1", "conv_fprop_14_256_256_3_1", "conv_fprop_28_128_128_3_2",
             "conv_dgrad_56_64_64_3_1", "conv_dgradacc_56_256_64_1_1", "conv_dgrad_56_128_128_3_2", "conv_wgrad_28_128_128_3_1",
             "conv_wgrad_56_64_256_1_1", "linear_8192x4096x4096", "bn_applyres_56_256", "bn_apply_56_64", "bn_bwdres_56_256",
-            "bn_bwd_56_64", "bn_stats_28_512", "maxpool", "avgpool", "stem", "sgd", "loss_ce", "allreduce_local"]
+            "bn_bwd_56_64", "bn_stats_28_512", "maxpool", "avgpool", "stem", "stem_implicit_fwd", "stem_implicit_wgrad", "stem_explicit", "sgd", "loss_ce", "allreduce_local"]
 
 if __name__ == "__main__":
     name = sys.argv[1]

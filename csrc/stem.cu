@@ -34,23 +34,51 @@ struct StemGeom {
   static constexpr int kPixels = kRowsOut * kStemTW;
 };
 
-// Stage the input window of one tile: image n, output rows oh0.., output columns ow0.. (all threads).
+// Input window of one tile, software-pipelined: every thread owns a fixed set of window elements (their
+// (row, col, channel) decomposition never changes, so no division per tile); `fetch` issues the global loads of
+// the NEXT tile into registers while the current tile is being built / multiplied, `store` writes them (as
+// bf16) into the staging buffer at the top of the next iteration.
 template <int kRowsOut>
-__device__ __forceinline__ void stem_stage_input(const float* __restrict__ x, unsigned short* stage, int n,
-                                                 int oh0, int ow0, int H, int W) {
+struct StemWindow {
   using G = StemGeom<kRowsOut>;
-  const int ih0 = 2 * oh0 - 3, iw0 = 2 * ow0 - 3;
-  const float* xn = x + (long long)n * 3 * H * W;
-  for (int i = threadIdx.x; i < G::kInRows * 3 * G::kInCols; i += kStemThreads) {
-    const int col = i % G::kInCols;
-    const int rc = i / G::kInCols;
-    const int c = rc % 3, r = rc / 3;
-    const int ih = ih0 + r, iw = iw0 + col;
-    float v = 0.f;
-    if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(xn + ((long long)c * H + ih) * W + iw);
-    stage[r * G::kPitch + col * 3 + c] = __bfloat16_as_ushort(__float2bfloat16(v));
+  static constexpr int kElems = G::kInRows * 3 * G::kInCols;
+  static constexpr int kPer = (kElems + kStemThreads - 1) / kStemThreads;
+  int rc[kPer];        // row << 8 | col   (-1: this thread has no such element)
+  int goff[kPer];      // (c * H + row) * W + col, relative to the window origin
+  int soff[kPer];      // staging offset row * pitch + col * 3 + c
+  float val[kPer];
+
+  __device__ __forceinline__ void init(int H, int W) {
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      const int i = threadIdx.x + j * kStemThreads;
+      if (i < kElems) {
+        const int col = i % G::kInCols, q = i / G::kInCols;
+        const int c = q % 3, r = q / 3;
+        rc[j] = (r << 8) | col;
+        goff[j] = (c * H + r) * W + col;
+        soff[j] = r * G::kPitch + col * 3 + c;
+      } else {
+        rc[j] = -1; goff[j] = 0; soff[j] = 0;
+      }
+    }
   }
-}
+  __device__ __forceinline__ void fetch(const float* __restrict__ x, int n, int oh0, int ow0, int H, int W) {
+    const int ih0 = 2 * oh0 - 3, iw0 = 2 * ow0 - 3;
+    const float* base = x + ((long long)n * 3 * H + ih0) * W + iw0;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      const int ih = ih0 + (rc[j] >> 8), iw = iw0 + (rc[j] & 255);
+      const bool ok = rc[j] >= 0 && ih >= 0 && ih < H && iw >= 0 && iw < W;
+      val[j] = ok ? __ldg(base + goff[j]) : 0.f;
+    }
+  }
+  __device__ __forceinline__ void store(unsigned short* stage) const {
+#pragma unroll
+    for (int j = 0; j < kPer; ++j)
+      if (rc[j] >= 0) stage[soff[j]] = __bfloat16_as_ushort(__float2bfloat16(val[j]));
+  }
+};
 
 // Build the patch tile [pixels][160] from the staged window into 64-element-wide, 128-byte-swizzled blocks:
 // block kb (k = 64*kb ..) starts at tile + kb * block_bytes, pixel row p at p * 128, 16-byte chunk (k%64)/8
@@ -105,7 +133,8 @@ __global__ void __launch_bounds__(kStemThreads, 2)
 stem_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, __nv_bfloat16* __restrict__ y,
                   float* bn_sums, int bn_reps, int det, int NB, int H, int W) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment for the swizzle atoms, computed as an OFFSET so the compiler keeps the shared address space
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = sA + kFwdABytes;
   uint8_t* sOut = sB + kFwdBBytes;
@@ -148,12 +177,23 @@ stem_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, __nv
 #pragma unroll
   for (int k = 0; k < 4; ++k) { sm2[k] = make_float2(0.f, 0.f); sq2[k] = make_float2(0.f, 0.f); }
   uint32_t phase = 0;
+  StemWindow<kFwdRows> win;
+  win.init(H, W);
+  if (blockIdx.x < ntiles) {
+    const int t = blockIdx.x;
+    win.fetch(x, t / (tiles_x * tiles_y), ((t / tiles_x) % tiles_y) * kFwdRows, (t % tiles_x) * kStemTW, H, W);
+  }
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int tx = t % tiles_x, ty = (t / tiles_x) % tiles_y, n = t / (tiles_x * tiles_y);
     const int oh0 = ty * kFwdRows, ow0 = tx * kStemTW;
-    stem_stage_input<kFwdRows>(x, stage, n, oh0, ow0, H, W);
+    win.store(stage);
     tc_fence_before();
     __syncthreads();              // window staged; last tile's TMEM reads and MMA operand reads are over
+    {
+      const int tn = t + gridDim.x;          // next tile's loads fly while this one is built and multiplied
+      if (tn < ntiles)
+        win.fetch(x, tn / (tiles_x * tiles_y), ((tn / tiles_x) % tiles_y) * kFwdRows, (tn % tiles_x) * kStemTW, H, W);
+    }
     stem_build_patch<kFwdRows>(stage, sA, 16384);
     fence_proxy_async();          // generic-proxy writes of the operand tile -> visible to the tensor core
     __syncthreads();
@@ -284,7 +324,8 @@ __global__ void __launch_bounds__(kStemThreads, 2)
 stem_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ dy, float* __restrict__ partial,
                   int NB, int H, int W) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment for the swizzle atoms, computed as an OFFSET so the compiler keeps the shared address space
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = sA + kWgABytes;
   unsigned short* stage = reinterpret_cast<unsigned short*>(sB + kWgBBytes);
@@ -307,23 +348,45 @@ stem_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__
   const uint32_t idesc = umma_idesc_bf16(128, 64, true, true);       // both operands MN-major
   uint32_t phase = 0;
   bool first = true;
+  StemWindow<kWgRows> win;
+  win.init(H, W);
+  uint4 dyv[2];                   // this thread's two 16-byte pieces of the next dy block
+  auto fetch_dy = [&](int tt) {
+    const int n = tt / (tiles_x * tiles_y), oh0 = ((tt / tiles_x) % tiles_y) * kWgRows, ow0 = (tt % tiles_x) * kStemTW;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int i = threadIdx.x + j * kStemThreads;
+      const int p = i >> 3, c = i & 7;
+      dyv[j] = ld_nc_v4(dy + ((((long long)n * Ho + oh0 + p / kStemTW) * Wo + ow0 + p % kStemTW) * 64 + c * 8));
+    }
+  };
+  if (blockIdx.x < nblocks) {
+    const int t = blockIdx.x;
+    win.fetch(x, t / (tiles_x * tiles_y), ((t / tiles_x) % tiles_y) * kWgRows, (t % tiles_x) * kStemTW, H, W);
+    fetch_dy(t);
+  }
   for (int t = blockIdx.x; t < nblocks; t += gridDim.x) {
-    const int tx = t % tiles_x, ty = (t / tiles_x) % tiles_y, n = t / (tiles_x * tiles_y);
-    const int oh0 = ty * kWgRows, ow0 = tx * kStemTW;
-    stem_stage_input<kWgRows>(x, stage, n, oh0, ow0, H, W);
+    win.store(stage);
     if (!first) {                 // the previous block's MMAs must have consumed sA / sB
       mbar_wait(&bars->mma_done, phase);
       phase ^= 1;
     }
     __syncthreads();
-    stem_build_patch<kWgRows>(stage, sA, 8192);
     // dy block: pixel p = (py, px) -> row p (128 B = 64 channels), chunk c XOR (p & 7)
-    for (int i = threadIdx.x; i < 64 * 8; i += kStemThreads) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int i = threadIdx.x + j * kStemThreads;
       const int p = i >> 3, c = i & 7;
-      const int py = p / kStemTW, px = p % kStemTW;
-      const uint4 u = ld_nc_v4(dy + ((((long long)n * Ho + oh0 + py) * Wo + ow0 + px) * 64 + c * 8));
-      *reinterpret_cast<uint4*>(sB + p * 128 + ((c ^ (p & 7)) << 4)) = u;
+      *reinterpret_cast<uint4*>(sB + p * 128 + ((c ^ (p & 7)) << 4)) = dyv[j];
     }
+    {
+      const int tn = t + gridDim.x;          // next block's loads fly while this one is built and multiplied
+      if (tn < nblocks) {
+        win.fetch(x, tn / (tiles_x * tiles_y), ((tn / tiles_x) % tiles_y) * kWgRows, (tn % tiles_x) * kStemTW, H, W);
+        fetch_dy(tn);
+      }
+    }
+    stem_build_patch<kWgRows>(stage, sA, 8192);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();

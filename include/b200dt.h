@@ -53,6 +53,16 @@ int b200dt_conv2d_dgrad_acc_bf16(const void* dy, const void* w, void* dx, int NB
 
 /* x: [NB,3,H,W] fp32 NCHW -> cols: [NB*Ho*Wo, ldk] bf16 with (r,s,c) ordering, 7x7 s2 p3. */
 int b200dt_stem_im2col(const float* x, void* cols, int NB, int H, int W, int ldk, void* stream);
+/* Implicit-GEMM stem (csrc/stem.cu): y[NB,H/2,W/2,64] bf16 NHWC = conv 7x7 s2 p3 of x[NB,3,H,W] fp32 NCHW with
+ * w[64,7,7,3] fp32; the patch matrix only ever exists tile by tile in shared memory. bn_sums as for the other
+ * convolutions (64 channels). Needs (W/2) % 16 == 0 and (H/2) % 8 == 0, else -3 (use im2col + GEMM). */
+int b200dt_stem_conv_fprop(const float* x, const float* w, void* y, int NB, int H, int W, float* bn_sums,
+                           void* stream);
+/* dw[64,7,7,3] fp32 from dy[NB,H/2,W/2,64] bf16; scratch: b200dt_stem_wgrad_scratch_floats() floats (one partial
+ * per CTA, folded in CTA order: the result is deterministic in every mode). */
+long long b200dt_stem_wgrad_scratch_floats(void);
+int b200dt_stem_conv_wgrad(const float* x, const void* dy, float* dw, float* scratch, int NB, int H, int W,
+                           void* stream);
 int b200dt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
 int b200dt_transpose_bf16(const void* src, void* dst, int rows, int cols, void* stream);
 int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, int W, void* stream);
@@ -160,7 +170,9 @@ int b200dt_ce_index_loss(const void* logits, const long long* labels, void* grad
  *    stream capture.
  *  - All calls on a device share the one array: two calls whose kernels may overlap on the GPU
  *    (different streams without ordering) race on it. Order them, or use b200dt_mse_loss with
- *    separate scratch buffers. The array lives on every GPU that loads the library until exit. */
+ *    separate scratch buffers. The array lives on every GPU that loads the library until exit.
+ *  - `stream` must belong to the device that is current when the call is made: the array used is the
+ *    current device's copy. The cached address does not survive cudaDeviceReset(). */
 #define B200DT_MSE_STATIC_SCRATCH_BYTES 1040
 #define B200DT_MSE_STATIC_MAX_ELEMS 1048576LL
 int b200dt_mse_loss_static(const void* pred, const void* target, void* grad, float* loss,

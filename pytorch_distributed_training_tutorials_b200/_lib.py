@@ -49,6 +49,8 @@ _SIGS = {
     "b200dt_conv2d_dgrad_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_conv2d_dgrad_acc_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp],
     "b200dt_stem_im2col": [vp, vp, i32, i32, i32, i32, vp],
+    "b200dt_stem_conv_fprop": [vp, vp, vp, i32, i32, i32, vp, vp],
+    "b200dt_stem_conv_wgrad": [vp, vp, vp, vp, i32, i32, i32, vp],
     "b200dt_cast_f32_to_bf16": [vp, vp, i64, vp],
     "b200dt_transpose_bf16": [vp, vp, i32, i32, vp],
     "b200dt_nchw_f32_to_nhwc_bf16": [vp, vp, i32, i32, i32, i32, vp],
@@ -123,6 +125,8 @@ def lib() -> "_Counted":
             fn.restype = i32
         handle.b200dt_loss_scratch_bytes.restype = i64
         handle.b200dt_loss_scratch_bytes.argtypes = []
+        handle.b200dt_stem_wgrad_scratch_floats.restype = i64
+        handle.b200dt_stem_wgrad_scratch_floats.argtypes = []
         handle.b200dt_coll_chunk_bytes.restype = i32
         handle.b200dt_coll_chunk_bytes.argtypes = []
         handle.b200dt_device_sm_count.restype = i32

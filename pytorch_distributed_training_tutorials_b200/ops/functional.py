@@ -8,9 +8,15 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 
 from . import native as NV
+
+# "implicit": the stem runs as an implicit GEMM (csrc/stem.cu, no patch matrix in memory); "im2col": explicit gather
+# + GEMM.  The default follows the measurements in profiles/ (B200DT_STEM overrides it).
+STEM_MODE = os.environ.get("B200DT_STEM", "im2col")
 
 BF16 = torch.bfloat16
 F32 = torch.float32
@@ -274,6 +280,19 @@ class _StemConv(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, with_stats):
         NB, _, H, W = x.shape
+        ctx.implicit = (STEM_MODE == "implicit" and weight.shape[0] == 64 and NV.stem_supported(x.shape)
+                        and x.dtype == F32)
+        if ctx.implicit:
+            # implicit GEMM: the patch matrix exists only tile by tile in shared memory (csrc/stem.cu)
+            xc = x.contiguous()
+            sums = NV.bn_sums_buffer(64, x.device) if with_stats else None
+            ctx.set_materialize_grads(False)
+            y = NV.stem_conv_fprop(xc, weight.detach().contiguous(), bn_sums=sums)
+            ctx.save_for_backward(xc, weight)
+            if with_stats:
+                ctx.mark_non_differentiable(sums)
+                return y, sums
+            return y
         cols = NV.stem_im2col(x.contiguous())
         wk = _stem_operand(weight)
         sums = NV.bn_sums_buffer(weight.shape[0], x.device) if with_stats else None
@@ -292,6 +311,10 @@ class _StemConv(torch.autograd.Function):
     def backward(ctx, dy, *unused):
         cols, weight = ctx.saved_tensors
         dw = None
+        if ctx.implicit:
+            if ctx.needs_input_grad[1] and dy is not None:
+                dw = NV.stem_conv_wgrad(cols, dy.contiguous())          # `cols` is the network input here
+            return None, dw, None
         if ctx.needs_input_grad[1] and dy is not None:
             dy2 = dy.reshape(-1, weight.shape[0]).contiguous()
             dwk = NV.gemm_nt_reduce(dy2, cols)               # [64, 160]

@@ -200,6 +200,35 @@ def stem_im2col(x: torch.Tensor) -> torch.Tensor:
     return cols
 
 
+def stem_supported(x_shape) -> bool:
+    """Shapes the implicit-GEMM stem takes: even H, W with (W/2) % 16 == 0 and (H/2) % 8 == 0 (224 and 128 do)."""
+    NB, C, H, W = x_shape
+    return C == 3 and H % 2 == 0 and W % 2 == 0 and (W // 2) % 16 == 0 and (H // 2) % 8 == 0
+
+
+def stem_conv_fprop(x: torch.Tensor, w: torch.Tensor, bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """7x7 s2 p3 stem: x [N,3,H,W] fp32 NCHW, w [64,7,7,3] fp32 -> [N,H/2,W/2,64] bf16 NHWC (no patch matrix)."""
+    _need(x, F32, "x"); _need(w, F32, "w")
+    NB, _, H, W = x.shape
+    assert tuple(w.shape) == (64, 7, 7, 3)
+    y = torch.empty((NB, H // 2, W // 2, 64), device=x.device, dtype=BF16)
+    with on_device(x.device):
+        check(lib().b200dt_stem_conv_fprop(ptr(x), ptr(w), ptr(y), NB, H, W, ptr(bn_sums), stream_ptr(x.device)),
+              "stem_conv_fprop")
+    return y
+
+
+def stem_conv_wgrad(x: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    _need(x, F32, "x"); _need(dy, BF16, "dy")
+    NB, _, H, W = x.shape
+    dw = torch.empty((64, 7, 7, 3), device=x.device, dtype=F32)
+    scratch = torch.empty(int(lib().b200dt_stem_wgrad_scratch_floats()), device=x.device, dtype=F32)
+    with on_device(x.device):
+        check(lib().b200dt_stem_conv_wgrad(ptr(x), ptr(dy), ptr(dw), ptr(scratch), NB, H, W, stream_ptr(x.device)),
+              "stem_conv_wgrad")
+    return dw
+
+
 def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     _need(src, F32, "src")
     if out is None:

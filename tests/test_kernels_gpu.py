@@ -406,3 +406,32 @@ def test_linear_with_an_output_width_that_is_not_a_multiple_of_8():
     (y * t).sum().backward(); (yr * t).sum().backward()
     for a, b in ((x.grad, xr.grad), (lin.weight.grad, ref.weight.grad), (lin.bias.grad, ref.bias.grad)):
         assert ((a - b).norm() / b.norm()).item() < 1e-2
+
+
+@pytest.mark.parametrize("nb,hw", [(4, 224), (3, 128), (2, 32)])
+def test_implicit_gemm_stem_matches_fp32_conv(nb, hw):
+    """7x7 stride-2 stem without a patch matrix: forward, fused BatchNorm statistics and the weight gradient against
+    torch's fp32 convolution on bf16-rounded operands; the weight gradient is bit-identical run to run."""
+    from pytorch_distributed_training_tutorials_b200.ops import native as NV
+    dev = torch.device("cuda:0")
+    torch.manual_seed(hw + nb)
+    x = torch.randn(nb, 3, hw, hw, device=dev)
+    w = torch.randn(64, 7, 7, 3, device=dev) * 0.1
+    assert NV.stem_supported(x.shape)
+    sums = NV.bn_sums_buffer(64, dev)
+    sums.fill_(float("nan"))
+    y = NV.stem_conv_fprop(x, w, bn_sums=sums)
+    xb, wb = x.bfloat16().float(), w.bfloat16().float()
+    ref = torch.nn.functional.conv2d(xb, wb.permute(0, 3, 1, 2), stride=2, padding=3).permute(0, 2, 3, 1)
+    assert y.shape == ref.shape
+    assert ((y.float() - ref).norm() / ref.norm()).item() < 5e-3
+    yf = y.float()
+    ref_s = torch.cat([yf.sum((0, 1, 2)), (yf * yf).sum((0, 1, 2))])
+    assert torch.allclose(sums[:128], ref_s, rtol=1e-4, atol=1e-2)
+    dy = torch.randn_like(y)
+    dw = NV.stem_conv_wgrad(x, dy)
+    dw2 = NV.stem_conv_wgrad(x, dy)
+    assert torch.equal(dw, dw2)
+    ref_dw = torch.nn.grad.conv2d_weight(xb, (64, 3, 7, 7), dy.float().permute(0, 3, 1, 2), stride=2,
+                                         padding=3).permute(0, 2, 3, 1)
+    assert ((dw - ref_dw).norm() / ref_dw.norm()).item() < 5e-3
