@@ -16,7 +16,7 @@ from . import native as NV
 
 # "implicit": the stem runs as an implicit GEMM (csrc/stem.cu, no patch matrix in memory); "im2col": explicit gather
 # + GEMM.  The default follows the measurements in profiles/ (B200DT_STEM overrides it).
-STEM_MODE = os.environ.get("B200DT_STEM", "im2col")
+STEM_MODE = os.environ.get("B200DT_STEM", "implicit")
 
 BF16 = torch.bfloat16
 F32 = torch.float32
