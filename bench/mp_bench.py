@@ -148,6 +148,35 @@ def main():
                     o.step()
             res[f"ours_pipelined_graphed_cut_layer1_split{split}"] = timed(train_graphed)
             del pipe, m, o
+        # the naive split and the single GPU, graph-replayed (same host-side input creation per batch)
+        m = ModelParallelResNet50(num_classes=num_classes); o = FusedSGD(m.parameters(), lr=1e-3)
+        ex_x = torch.randn(batch_size, 3, image_w, image_h, device="cuda:0")
+        ex_y = torch.zeros(batch_size, num_classes, device="cuda:1")
+        pipe = m.graphed(Fn.mse_loss, ex_x, ex_y)
+
+        def train_naive_graphed():
+            for _ in range(num_batches):
+                inputs = torch.randn(batch_size, 3, image_w, image_h)
+                labels = torch.zeros(batch_size, num_classes).scatter_(1, idx, 1)
+                pipe.zero_grad()
+                pipe.train_step(inputs, labels)
+                o.step()
+        res["ours_naive_mp_graphed"] = timed(train_naive_graphed)
+        del pipe, m, o
+    from pytorch_distributed_training_tutorials_b200.utils.graph import GraphedTrainStep
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn2
+    m = resnet50(num_classes=num_classes).to("cuda:0"); o = FusedSGD(m.parameters(), lr=1e-3)
+    g = GraphedTrainStep(m, Fn2.mse_loss, o, torch.randn(batch_size, 3, image_w, image_h, device="cuda:0"),
+                         torch.zeros(batch_size, num_classes, device="cuda:0"))
+    idx1 = torch.LongTensor(batch_size).random_(0, num_classes).view(batch_size, 1)
+
+    def train_single_graphed():
+        for _ in range(num_batches):
+            inputs = torch.randn(batch_size, 3, image_w, image_h)
+            labels = torch.zeros(batch_size, num_classes).scatter_(1, idx1, 1)
+            g(inputs.to("cuda:0"), labels.to("cuda:0"))
+    res["ours_single_gpu_graphed"] = timed(train_single_graphed)
+    del g, m, o
     ns = reference_cells()
     if ns is not None:
         import torchvision.models as models

@@ -42,6 +42,15 @@ class ModelParallelResNet50(ResNet):
     def forward(self, x):
         return self.stage1(hop(self.stage0(x.to(self.dev0)), self.dev1))
 
+    def graphed(self, loss_fn, example_x: torch.Tensor, example_y: torch.Tensor, chunks: int = 1):
+        """CUDA-graph replayed training step of this split (``parallel.graphed_pipeline``): forward + loss +
+        backward of both stages are captured once and a step is a handful of graph launches, so the host stops
+        being the bottleneck (the notebook's 120 x 128^2 batches are launch-bound in eager mode on a B200).
+        ``chunks=1`` is the naive split; returns an object with ``train_step(x, y)`` / ``zero_grad()``."""
+        from ..parallel.graphed_pipeline import GraphedPipeline
+        return GraphedPipeline([self.stage0, self.stage1], [self.dev0, self.dev1], chunks, loss_fn,
+                               example_x, example_y, parameters=list(self.parameters()))
+
 
 class PipelineParallelResNet50(ModelParallelResNet50):
     def __init__(self, split_size: int = 20, **kw) -> None:
@@ -61,10 +70,7 @@ class PipelineParallelResNet50(ModelParallelResNet50):
         outs.append(self.stage1(prev))
         return torch.cat(outs, dim=0)
 
-    def graphed(self, loss_fn, example_x: torch.Tensor, example_y: torch.Tensor):
-        """CUDA-graph replayed training step for this split (``parallel.graphed_pipeline``): the
-        micro-batch count is ``batch // split_size``; returns an object with ``train_step(x, y)``."""
-        from ..parallel.graphed_pipeline import GraphedPipeline
-        chunks = max(1, example_x.shape[0] // self.split_size)
-        return GraphedPipeline([self.stage0, self.stage1], [self.dev0, self.dev1], chunks, loss_fn,
-                               example_x, example_y, parameters=list(self.parameters()))
+    def graphed(self, loss_fn, example_x: torch.Tensor, example_y: torch.Tensor, chunks: int = 0):
+        """Graph-replayed micro-batch pipeline; the micro-batch count defaults to ``batch // split_size``."""
+        return super().graphed(loss_fn, example_x, example_y,
+                               chunks or max(1, example_x.shape[0] // self.split_size))
