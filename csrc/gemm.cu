@@ -69,6 +69,11 @@ struct GemmParams {
   // step[] are the digits of gridDim.x, i.e. what one iteration of the persistent loop adds.
   int rad[3];
   int step[4];
+  // Halo mode (3x3, stride 1, Cin == Cout == 64): ONE TMA box of (bw+2) x (bh+2) pixels is staged per tile and the
+  // nine taps are nine shifted operand views of it (descriptor start = any 128-byte row, 8-row groups (bw+2)*128
+  // bytes apart: the swizzle is a function of the absolute shared address, bench/probes/umma_shift_probe.cu);
+  // the 9 x 64 x 64 filter stays resident in shared memory for the whole kernel.
+  int halo;
   const float* bias;
   // deterministic mode (b200::deterministic()): sums are combined in a fixed order
   int det;                  // 1: no floating-point atomics anywhere in this launch
@@ -87,6 +92,7 @@ struct alignas(8) Barriers {
   uint64_t empty[8];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t wfull;
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -162,7 +168,10 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int a_stage_bytes = kBM * kBK * 2;            // 16 KB
   const int b_stage_bytes = p.BN * kBK * 2;           // 8..32 KB
-  const int stage_bytes = a_stage_bytes + b_stage_bytes;
+  constexpr int kHaloW = 9 * 8192;                     // resident filter: 9 taps x (64 x 64) bf16
+  constexpr int kHaloStage = 23 * 1024;                // (8+2) x (16+2) pixels x 128 B = 23040, rounded to 1 KB
+  const int stage_bytes = p.halo ? kHaloStage : a_stage_bytes + b_stage_bytes;
+  if (p.halo) smem += kHaloW;                          // stages follow the resident filter
   uint8_t* stage_out = smem + p.stages * stage_bytes;          // 2 x 16 KB epilogue staging
   float* col_acc = reinterpret_cast<float*>(stage_out + 2 * kStageOutBytes);     // [4 quarters][2][256]
   Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes + p.colacc_bytes);
@@ -183,6 +192,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       mbar_init(&bars->tmem_full[i], 1);
       mbar_init(&bars->tmem_empty[i], 8);        // one arrive per epilogue warp
     }
+    mbar_init(&bars->wfull, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -205,6 +215,24 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       uint32_t phase = 0;
       TileCoord tc;
       tile_init(p, blockIdx.x, tc);
+      if (p.halo) {
+        // resident filter: nine 64 x 64 blocks, loaded once per CTA
+        const uint32_t sw0 = smem0 - kHaloW, wb = smem_u32(&bars->wfull);
+        mbar_expect_tx_s(wb, kHaloW);
+        for (int tap = 0; tap < 9; ++tap) {
+          if (!p.b_mn) tma_load_2d_s(sw0 + tap * 8192, &maps.b[0], wb, tap * 64, 0);
+          else tma_load_2d_s(sw0 + tap * 8192, &maps.b[0], wb, p.taps[tap].pad * 64, 0);
+        }
+        const uint32_t tx = (uint32_t)((p.bw + 2) * (p.bh + 2) * 128);
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
+          mbar_wait(&bars->empty[stage], phase ^ 1);
+          const uint32_t fb = full0 + stage * 8;
+          mbar_expect_tx_s(fb, tx);
+          // one box with a one-pixel halo all around; outside the image TMA fills zeros (= the padding)
+          tma_load_4d_s(smem0 + stage * stage_bytes, &maps.a[1], fb, 0, tc.d1 * p.bw - 1, tc.d2 * p.bh - 1, tc.d3);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      } else
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
         const int n_blk = tc.d0;
         const int m_blk = tc.d1;                          // kind 1 only
@@ -297,6 +325,13 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       const uint32_t idesc = umma_idesc_bf16(kBM, p.BN, a_mn, b_mn);
       const uint32_t lbo_a = a_mn ? 8192u : 16u, lbo_b = b_mn ? 8192u : 16u;
       const uint32_t kstep_a = a_mn ? 2048u : 32u, kstep_b = b_mn ? 2048u : 32u;
+      const uint32_t smem0_mma = smem_u32(smem);
+      const uint64_t desc_a0 = umma_desc_sw128(0, lbo_a, p.halo ? (uint32_t)(p.bw + 2) * 128u : 1024u);
+      const uint64_t desc_b0 = umma_desc_sw128(0, lbo_b, 1024);
+      uint32_t halo_aoff[9];                   // (row offset of tap's view inside the staged patch) >> 4
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap)
+        halo_aoff[tap] = (uint32_t)((p.taps[tap].dh + 1) * (p.bw + 2) + (p.taps[tap].dw + 1)) * 8u;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -310,17 +345,33 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * p.BN;
+        if (p.halo) {
+          if (t == (int)blockIdx.x) { mbar_wait(&bars->wfull, 0); tc_fence_after(); }
+          mbar_wait(&bars->full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = (smem0_mma + stage * stage_bytes) >> 4;
+          const uint32_t sw0 = (smem0_mma - kHaloW) >> 4;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            // the tap's operand = the staged patch seen from pixel (dh + 1, dw + 1)
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k)
+              umma_f16(tmem_d, desc_a0 + (sa + halo_aoff[tap] + k * 2), desc_b0 + (sw0 + tap * 512 + k * (kstep_b >> 4)),
+                       idesc, (tap > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&bars->empty[stage]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        } else
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&bars->full[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-          const uint32_t sb = sa + a_stage_bytes;
+          // descriptor = constant high part + (shared address >> 4): one add per operand per instruction
+          const uint32_t sa = (smem0_mma + stage * stage_bytes) >> 4;
+          const uint32_t sb = sa + (a_stage_bytes >> 4);
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            const uint64_t da = umma_desc_sw128(sa + k * kstep_a, lbo_a, 1024);
-            const uint64_t db = umma_desc_sw128(sb + k * kstep_b, lbo_b, 1024);
-            umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < kBK / 16; ++k)
+            umma_f16(tmem_d, desc_a0 + (sa + k * (kstep_a >> 4)), desc_b0 + (sb + k * (kstep_b >> 4)), idesc,
+                     (kb > kb0 || k > 0) ? 1u : 0u);
           umma_commit(&bars->empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -363,6 +414,9 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         }
         uint8_t* my_row = buf + lane * 128;
         const int sw = lane & 7;
+        // halo tiles may hang over the image edge: those rows are clipped by the TMA store, but they must not
+        // enter the fused statistics (their 3x3 windows still touch valid pixels), so they are staged as zeros
+        const bool zero_row = p.halo && (th * p.bh + row / p.bw >= p.H || tw * p.bw + row % p.bw >= p.W);
         const bool plain = (p.bias == nullptr) && !p.relu;       // uniform across the CTA
         for (int sl = pi; sl < nslabs; sl += 2) {
           const int col0 = col_base + sl * cols_per_slab;
@@ -412,6 +466,10 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             __syncwarp();
             tmem_ld_wait();
+            if (zero_row) {                    // (halo tiles only, edge rows only: skipped by whole warps otherwise)
+#pragma unroll
+              for (int j = 0; j < 32; ++j) { v0[j] = 0u; v1[j] = 0u; }
+            }
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
               const uint32_t* v = half ? v1 : v0;
@@ -696,9 +754,10 @@ static int num_sms() {
 
 static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMaxMaps],
                   const CUtensorMap* mapC, GemmParams& p, cudaStream_t stream) {
-  const int stage_bytes = kBM * kBK * 2 + p.BN * kBK * 2;
+  const int stage_bytes = p.halo ? 23 * 1024 : kBM * kBK * 2 + p.BN * kBK * 2;
   p.colacc_bytes = p.bn_sums != nullptr ? kColAccBytes : 0;
-  const int fixed = 2 * kStageOutBytes + p.colacc_bytes + (int)sizeof(Barriers) + 64;
+  const int halo_w = p.halo ? 9 * 8192 : 0;
+  const int fixed = 2 * kStageOutBytes + p.colacc_bytes + (int)sizeof(Barriers) + 64 + halo_w;
   int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return -2;
@@ -822,6 +881,23 @@ static int det_split_end(const GemmParams& p, float* part, int ld_s, float* out,
   cudaError_t e = cudaGetLastError();
   cudaError_t f = cudaFreeAsync(part, st);
   return (int)(e != cudaSuccess ? e : f);
+}
+
+// Halo mode applies to the 3x3 stride-1 64 -> 64 convolutions (ResNet layer1): B200DT_HALO=0 switches it off.
+static bool halo_shape(int R, int stride, int Cin, int Cout) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("B200DT_HALO");
+    enabled = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return enabled && R == 3 && stride == 1 && Cin == 64 && Cout == 64;
+}
+static void halo_tiling(GemmParams& p, int Wo, int Ho, int NB) {
+  p.halo = 1;
+  p.bw = 8; p.bh = 16; p.bn = 1;                 // 8-pixel row groups: one UMMA core-matrix group per output row
+  p.tiles_w = (Wo + 7) / 8;
+  p.tiles_h = (Ho + 15) / 16;                    // edge tiles hang over the image: zero fill in, clipped stores out
+  p.tiles_m = p.tiles_w * p.tiles_h * NB;
 }
 
 }  // namespace b200
@@ -976,6 +1052,8 @@ extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, i
   p.tiles_h = Ho / p.bh;
   const int tiles_nb = (NB + p.bn - 1) / p.bn;
   p.tiles_m = p.tiles_w * p.tiles_h * tiles_nb;
+  const bool halo = halo_shape(R, stride, Cin, Cout);
+  if (halo) halo_tiling(p, Wo, Ho, NB);
   p.tiles_n = (Cout + p.BN - 1) / p.BN;
   p.splits = 1;
   p.cin_blocks = Cin / 64;
@@ -997,6 +1075,11 @@ extern "C" int b200dt_conv2d_fprop_bf16(const void* x, const void* w, void* y, i
     r = make_map4(&ma[0], xb, dims, str, box);
     if (r) return r;
     ma[1] = ma[2] = ma[3] = ma[0];
+    if (halo) {
+      int hbox[4] = {64, p.bw + 2, p.bh + 2, 1};
+      r = make_map4(&ma[1], xb, dims, str, hbox);
+      if (r) return r;
+    }
     const int pad = R / 2;
     for (int rr = 0; rr < R; ++rr)
       for (int ss = 0; ss < R; ++ss)
@@ -1170,6 +1253,8 @@ static int conv2d_dgrad_impl(const void* dy, const void* w, void* dx, int NB, in
       pick_box(Wo, Ho, 128, &p.bw, &p.bh, &p.bn);
       p.tiles_w = Wo / p.bw; p.tiles_h = Ho / p.bh;
       p.tiles_m = p.tiles_w * p.tiles_h * ((NB + p.bn - 1) / p.bn);
+      const bool halo = halo_shape(R, stride, Cin, Cout);
+      if (halo) halo_tiling(p, Wo, Ho, NB);
       p.tiles_n = (Cin + p.BN - 1) / p.BN;
       p.splits = 1;
       p.cin_blocks = (Cout + 63) / 64;
@@ -1204,6 +1289,11 @@ static int conv2d_dgrad_impl(const void* dy, const void* w, void* dx, int NB, in
       int r = make_map4(&ma[0], dy, dims, str, box);
       if (r) return r;
       ma[1] = ma[2] = ma[3] = ma[0];
+      if (halo) {
+        int hbox[4] = {64, p.bw + 2, p.bh + 2, 1};
+        r = make_map4(&ma[1], dy, dims, str, hbox);
+        if (r) return r;
+      }
       // B = w viewed as [Cout rows][R*R*Cin columns]; a chunk is 64 columns x 64 rows
       r = make_map2(&mb[0], w, (long long)R * R * Cin, Cout, (long long)R * R * Cin, 64, 64);
       if (r) return r;

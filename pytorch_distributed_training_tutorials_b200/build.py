@@ -55,7 +55,9 @@ def kernel_sources():
 
 
 def lib_path() -> Path:
-    return NATIVE / "libb200dt.so"
+    # B200DT_LIB: load another build of the kernel library (A/B measurements of kernel changes on one box)
+    override = os.environ.get("B200DT_LIB")
+    return Path(override) if override else NATIVE / "libb200dt.so"
 
 
 def build_kernels(force: bool = False, verbose: bool = False) -> Path:

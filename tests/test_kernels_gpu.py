@@ -435,3 +435,31 @@ def test_implicit_gemm_stem_matches_fp32_conv(nb, hw):
     ref_dw = torch.nn.grad.conv2d_weight(xb, (64, 3, 7, 7), dy.float().permute(0, 3, 1, 2), stride=2,
                                          padding=3).permute(0, 2, 3, 1)
     assert ((dw - ref_dw).norm() / ref_dw.norm()).item() < 5e-3
+
+
+@pytest.mark.parametrize("nb,H", [(3, 56), (2, 28), (5, 12), (1, 16), (2, 7)])
+def test_halo_reuse_3x3_64_to_64(nb, H):
+    """3x3 / stride 1 / 64 -> 64 runs in halo mode (one staged patch, nine shifted operand views, resident filter).
+    Tiles of 8 x 16 pixels hang over the image edge when H or W is not a multiple: forward, fused statistics, data
+    gradient and accumulating data gradient against fp32 torch."""
+    from pytorch_distributed_training_tutorials_b200.ops import native as NV
+    dev = torch.device("cuda:0")
+    torch.manual_seed(H * 10 + nb)
+    x = torch.randn(nb, H, H, 64, device=dev).to(torch.bfloat16)
+    w = (torch.randn(64, 3, 3, 64, device=dev) * 0.06).to(torch.bfloat16)
+    dy = torch.randn(nb, H, H, 64, device=dev).to(torch.bfloat16)
+    sums = NV.bn_sums_buffer(64, dev)
+    sums.fill_(float("nan"))
+    y = NV.conv2d_fprop(x, w, bn_sums=sums)
+    xf, wf = x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2)
+    ref = torch.nn.functional.conv2d(xf, wf, padding=1).permute(0, 2, 3, 1)
+    assert ((y.float() - ref).norm() / ref.norm()).item() < 5e-3
+    yf = y.float()
+    ref_s = torch.cat([yf.sum((0, 1, 2)), (yf * yf).sum((0, 1, 2))])
+    assert torch.allclose(sums[:128], ref_s, rtol=1e-4, atol=1e-2)
+    dx = NV.conv2d_dgrad(dy, w, x.shape, 3)
+    ref_dx = torch.nn.grad.conv2d_input(xf.shape, wf, dy.float().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
+    assert ((dx.float() - ref_dx).norm() / ref_dx.norm()).item() < 5e-3
+    skip = torch.randn_like(x)
+    acc = NV.conv2d_dgrad(dy, w, x.shape, 3, accumulate_into=skip.clone())
+    assert ((acc.float() - (skip.float() + ref_dx)).norm() / ref_dx.norm()).item() < 1e-2
