@@ -1,6 +1,9 @@
 """Single-process 2-GPU ResNet-50: naive split vs eager pipeline vs CUDA-graph replayed pipeline.
 
-    python bench/graphed_pipeline_bench.py [--batch 512 --chunks 1,2,4,8 --cut layer1,layer2]
+    python bench/graphed_pipeline_bench.py [--batch 512 --chunks 1,2,4,8 --cut layer1,layer2,balanced,layer2.1]
+
+A cut is any unit of ``ResNet.unit_names()`` (whole layers or single bottleneck blocks); ``balanced`` lets
+``ModelParallelResNet50.balanced`` measure the units and pick the cut.  ``--no-eager`` skips the eager variants.
 
 Every variant runs zero_grad + forward + loss + backward + FusedSGD step on the same device-resident
 mini-batch; device-timed with CUDA events on cuda:0 after synchronising both GPUs. BASELINE.json config 4.
@@ -42,6 +45,7 @@ def main():
     ap.add_argument("--chunks", type=str, default="1,2,4,8")
     ap.add_argument("--cut", type=str, default="layer1,layer2")
     ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--no-eager", action="store_true")
     args = ap.parse_args()
     B = args.batch
     two = torch.cuda.device_count() >= 2
@@ -61,17 +65,24 @@ def main():
     print(json.dumps(res), flush=True)
 
     for cut in args.cut.split(","):
-        mp = ModelParallelResNet50(dev0=d0, dev1=d1, split_after=cut); o = b2.FusedSGD(mp.parameters(), lr=1e-3)
-        def naive():
-            o.zero_grad(); Fn.cross_entropy(mp(x), y).backward(); o.step()
-        res[f"cut_{cut}/naive_eager_ms"] = timed(naive, args.steps)
-        del mp, o
+        if cut != "balanced" and not args.no_eager:
+            mp = ModelParallelResNet50(dev0=d0, dev1=d1, split_after=cut); o = b2.FusedSGD(mp.parameters(), lr=1e-3)
+            def naive():
+                o.zero_grad(); Fn.cross_entropy(mp(x), y).backward(); o.step()
+            res[f"cut_{cut}/naive_eager_ms"] = timed(naive, args.steps)
+            del mp, o
         for ch in [int(c) for c in args.chunks.split(",")]:
             if B % ch:
                 continue
-            pm = PipelineParallelResNet50(split_size=B // ch, dev0=d0, dev1=d1, split_after=cut)
+            if cut == "balanced":
+                pm = PipelineParallelResNet50.balanced(x, chunks=ch, split_size=B // ch, dev0=d0, dev1=d1)
+                res[f"cut_balanced/chunks{ch}_chosen"] = pm.split_after
+                res[f"cut_balanced/chunks{ch}_unit_ms"] = {k: round(v, 3) for k, v in pm.unit_times_ms.items()}
+                print(f"balanced cut for {ch} chunks: after {pm.split_after}", flush=True)
+            else:
+                pm = PipelineParallelResNet50(split_size=B // ch, dev0=d0, dev1=d1, split_after=cut)
             o = b2.FusedSGD(pm.parameters(), lr=1e-3)
-            if ch > 1:
+            if ch > 1 and not args.no_eager:
                 def eager():
                     o.zero_grad(); Fn.cross_entropy(pm(x), y).backward(); o.step()
                 res[f"cut_{cut}/pipeline_eager_chunks{ch}_ms"] = timed(eager, args.steps)

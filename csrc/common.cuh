@@ -51,6 +51,34 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return red[0];
 }
 
+// Last-CTA fold of the partial-sum copies behind a BatchNorm `sums` buffer: copy 0 = sum over copies
+// 0..nrep-1 (ascending: a fixed order) of n floats each (n % 4 == 0, 16-byte aligned copies, stride n).
+// 16-byte L2 loads, eight in flight per thread: the fold used to be a serial chain of scalar loads on one
+// CTA and cost 20-40 us per launch on the 1024/2048-channel layers.
+__device__ __forceinline__ void fold_sum_copies(float* sums, int n, int nrep, int tid, int nthreads) {
+  if (n & 3) {                                       // odd channel counts (never a conv): scalar loads
+    for (int i = tid; i < n; i += nthreads) {
+      float t = 0.f;
+      for (int r = 0; r < nrep; ++r) t += __ldcg(sums + (size_t)r * n + i);
+      sums[i] = t;
+    }
+    return;
+  }
+  for (int i = tid * 4; i < n; i += nthreads * 4) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r0 = 0; r0 < nrep; r0 += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        v[u] = (r0 + u < nrep) ? __ldcg(reinterpret_cast<const float4*>(sums + (size_t)(r0 + u) * n + i))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { t.x += v[u].x; t.y += v[u].y; t.z += v[u].z; t.w += v[u].w; }
+    }
+    *reinterpret_cast<float4*>(sums + i) = t;
+  }
+}
+
 inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
 // Library-wide switches (csrc/config.cu).  deterministic(): every floating-point sum that is normally
@@ -60,5 +88,8 @@ int deterministic();
 // Copies of the partial-sum array behind a BatchNorm `sums` buffer: B200DT_BN_REPLICAS normally, one
 // per possible CTA slot (B200DT_BN_REPLICAS_DET) in deterministic mode.
 int bn_replicas();
+// copies a C-channel reduction spreads its atomics over (<= bn_replicas(); the ticket word stays behind
+// bn_replicas() copies, which is what callers allocate)
+int bn_replicas_used(int C);
 
 }  // namespace b200

@@ -22,6 +22,16 @@ int deterministic() {
 
 int bn_replicas() { return deterministic() ? B200DT_BN_REPLICAS_DET : B200DT_BN_REPLICAS; }
 
+// Copies actually spread over by the atomics of a C-channel reduction: the contention per address falls with
+// the channel count (the CTAs are divided among more column groups), and the last CTA's fold costs
+// 2 * C * copies loads, so wide layers use few copies (2048 channels: one, and no fold at all).
+int bn_replicas_used(int C) {
+  if (deterministic()) return B200DT_BN_REPLICAS_DET;
+  int r = 2048 / (C > 0 ? C : 1);
+  if (r < 1) r = 1;
+  return r > B200DT_BN_REPLICAS ? B200DT_BN_REPLICAS : r;
+}
+
 }  // namespace b200
 
 extern "C" void b200dt_set_deterministic(int on) { b200::g_det.store(on ? 1 : 0, std::memory_order_relaxed); }

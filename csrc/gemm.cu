@@ -78,6 +78,7 @@ struct GemmParams {
   // deterministic mode (b200::deterministic()): sums are combined in a fixed order
   int det;                  // 1: no floating-point atomics anywhere in this launch
   int bn_reps;              // copies of {sum, sumsq}[bn_C] behind bn_sums (ticket word follows them)
+  int bn_used;              // copies the atomics are spread over (<= bn_reps; 1: no ticket, no fold)
   long long split_stride;   // WGRAD, det: split s writes its partial tile to C + s * split_stride
 };
 
@@ -606,7 +607,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         float* accb = col_acc;
         // det: this CTA owns copy blockIdx.x and column c is always handled by the same thread, so a
         // plain read-modify-write in tile order replaces the atomics
-        float* dstb = p.bn_sums + (size_t)(p.det ? blockIdx.x : blockIdx.x % p.bn_reps) * 2 * p.bn_C;
+        float* dstb = p.bn_sums + (size_t)(p.det ? blockIdx.x : blockIdx.x % p.bn_used) * 2 * p.bn_C;
         const int e = (warp - 2) * 32 + lane;          // 0..255: one column per thread
         if (e < p.BN) {
           const int c = col_base + e;
@@ -623,7 +624,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (p.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    if (p.bn_sums != nullptr) {
+    if (p.bn_sums != nullptr && (p.det || p.bn_used > 1)) {
       // the last CTA to get here folds the replicas into copy 0 (what bn_apply reads)
       __threadfence();
       asm volatile("bar.sync 2, 256;" ::: "memory");
@@ -640,14 +641,8 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
           : "=r"(fold_last) : "r"(mine) : "memory");
       if (fold_last) {
         __threadfence();
-        for (int i = threadIdx.x - 64; i < 2 * p.bn_C; i += 256) {
-          float tsum = 0.f;
-          const int nrep = p.det ? min(p.bn_reps, (int)gridDim.x) : p.bn_reps;
-#pragma unroll 4
-          for (int r = 0; r < nrep; ++r)
-            tsum += *reinterpret_cast<volatile float*>(p.bn_sums + (size_t)r * 2 * p.bn_C + i);
-          p.bn_sums[i] = tsum;
-        }
+        fold_sum_copies(p.bn_sums, 2 * p.bn_C, p.det ? min(p.bn_reps, (int)gridDim.x) : p.bn_used,
+                        (int)threadIdx.x - 64, 256);
       }
     }
   }
@@ -765,6 +760,7 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   p.tma_store = mapC != nullptr ? 1 : 0;
   p.det = deterministic();
   p.bn_reps = bn_replicas();
+  p.bn_used = p.bn_sums != nullptr ? bn_replicas_used(p.bn_C) : 1;
 
   const int smem = stages * stage_bytes + fixed;
   // function attributes are per device: opt in to the large dynamic smem once on each
@@ -907,6 +903,8 @@ using namespace b200;
 // C[M,N] (bf16 or fp32) = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU)     -- all row-major, bf16 inputs.
 static int clear_bn_sums(float* bn_sums, int C, cudaStream_t st) {
   if (bn_sums == nullptr) return 0;
+  if (!deterministic() && bn_replicas_used(C) == 1)       // one copy, no ticket (see the fold in the kernel)
+    return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * (size_t)2 * C, st);
   return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * bn_replicas() + 1), st);
 }
 

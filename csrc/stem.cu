@@ -302,12 +302,9 @@ stem_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, __nv
     is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
   }
   __syncthreads();
-  if (is_last && threadIdx.x < 128) {
+  if (is_last) {
     __threadfence();
-    float tsum = 0.f;
-    const int nrep = det ? min(bn_reps, (int)gridDim.x) : bn_reps;
-    for (int r = 0; r < nrep; ++r) tsum += *reinterpret_cast<volatile float*>(bn_sums + (size_t)r * 128 + threadIdx.x);
-    bn_sums[threadIdx.x] = tsum;
+    fold_sum_copies(bn_sums, 128, det ? min(bn_reps, (int)gridDim.x) : bn_reps, threadIdx.x, blockDim.x);
   }
 }
 

@@ -107,6 +107,42 @@ class ResNet(nn.Module):
             x = self.run_segment(name, x)
         return x
 
+    # ---- block-level units: the stem, every bottleneck block, the global pool.  Pipeline cuts may fall between
+    # any two of them (``"layer2.1"`` = after the second block of layer2); a whole-layer name is its last block.
+    def unit_names(self) -> List[str]:
+        names = ["stem"]
+        for layer in self.SEGMENTS[1:5]:
+            names += [f"{layer}.{b}" for b in range(len(getattr(self, layer)))]
+        return names + ["pool"]
+
+    def unit_index(self, name: str, last: bool = True) -> int:
+        names = self.unit_names()
+        if name in names:
+            return names.index(name)
+        if name in self.SEGMENTS[1:5]:
+            return names.index(f"{name}.{len(getattr(self, name)) - 1 if last else 0}")
+        raise ValueError(f"unknown unit {name!r}; choose from {names} or a whole layer name")
+
+    def unit_modules(self, name: str) -> List[nn.Module]:
+        if name == "stem":
+            return [self.conv1, self.bn1, self.maxpool]
+        if name == "pool":
+            return [self.avgpool]
+        layer, b = name.split(".")
+        return [getattr(self, layer)[int(b)]]
+
+    def run_unit(self, name: str, x: torch.Tensor) -> torch.Tensor:
+        if "." in name:
+            layer, b = name.split(".")
+            return getattr(self, layer)[int(b)](x)
+        return self.run_segment(name, x)
+
+    def run_units(self, x: torch.Tensor, first: int, last: int) -> torch.Tensor:
+        """Run units ``first .. last`` (inclusive indices into ``unit_names()``)."""
+        for name in self.unit_names()[first:last + 1]:
+            x = self.run_unit(name, x)
+        return x
+
     def features_stage0(self, x: torch.Tensor) -> torch.Tensor:
         """conv1 .. layer2 (the reference's ``seq1``, 03.model_parallel.ipynb:812-819)."""
         return self.run_segments(x, "stem", "layer2")

@@ -15,29 +15,51 @@ from .resnet import ResNet
 
 
 class ModelParallelResNet50(ResNet):
-    """``split_after`` names the last segment that lives on the first device.  ``"layer2"`` is the
-    reference's split; on B200 the high-resolution half (stem .. layer2) takes ~70 % of the step time
-    with these kernels, so ``"layer1"`` gives the better balanced pipeline."""
+    """``split_after`` names the last unit that lives on the first device: a whole segment (``"stem"``,
+    ``"layer1"`` .. ``"layer3"``) or one bottleneck block (``"layer2.1"``, see ``ResNet.unit_names``).
+    ``"layer2"`` is the reference's split; on B200 the high-resolution half (stem .. layer2) takes ~70 % of the
+    step time with these kernels, so a pipeline wants the cut inside layer2: ``balanced()`` measures it."""
 
     def __init__(self, num_classes: int = 1000, dev0="cuda:0", dev1="cuda:1", split_after: str = "layer2") -> None:
         super().__init__([3, 4, 6, 3], num_classes=num_classes)
         self.dev0, self.dev1 = torch.device(dev0), torch.device(dev1)
-        assert split_after in ("stem", "layer1", "layer2", "layer3")
-        self.split_after = split_after
-        cut = self.SEGMENTS.index(split_after)
-        self._next = self.SEGMENTS[cut + 1]
-        on0 = {"stem": (self.conv1, self.bn1, self.maxpool), "layer1": (self.layer1,), "layer2": (self.layer2,),
-               "layer3": (self.layer3,), "layer4": (self.layer4,), "pool": (self.avgpool,)}
-        for i, seg in enumerate(self.SEGMENTS):
-            for mod in on0[seg]:
+        names = self.unit_names()
+        cut = self.unit_index(split_after)
+        if not 0 <= cut < len(names) - 1:
+            raise ValueError(f"split_after={split_after!r} leaves nothing for the second device")
+        self.split_after, self._cut, self._last = split_after, cut, len(names) - 1
+        for i, name in enumerate(names):
+            for mod in self.unit_modules(name):
                 mod.to(self.dev0 if i <= cut else self.dev1)
         self.fc.to(self.dev1)
 
+    @classmethod
+    def balanced(cls, example_x: torch.Tensor, chunks: int = 1, reps: int = 3, **kw):
+        """Build the split whose slower stage is fastest: times forward + backward of every unit on one
+        micro-batch (``example_x[: batch // chunks]``) on ``dev0`` and cuts where the two halves are closest
+        (``parallel.place.profile_units`` / ``balanced_cuts``).  The measured times are kept in
+        ``unit_times_ms`` on the returned model."""
+        from ..parallel.place import balanced_cuts, profile_units
+        dev0 = torch.device(kw.get("dev0", "cuda:0"))
+        probe = ResNet([3, 4, 6, 3], num_classes=kw.get("num_classes", 1000)).to(dev0)
+        names = probe.unit_names()
+        units = [lambda t, n=n: probe.run_unit(n, t) for n in names]
+        units[-1] = lambda t: probe.fc(probe.run_unit("pool", t))
+        mb = example_x[: max(1, example_x.shape[0] // chunks)].to(dev0)
+        times = profile_units(units, mb, reps=reps, module=probe)
+        del probe, units
+        torch.cuda.empty_cache()
+        cut = balanced_cuts(times, 2)[0]
+        cut = min(cut, len(names) - 2)
+        model = cls(split_after=names[cut], **kw)
+        model.unit_times_ms = dict(zip(names, times))
+        return model
+
     def stage0(self, x):
-        return self.run_segments(x, "stem", self.split_after)
+        return self.run_units(x, 0, self._cut)
 
     def stage1(self, x):
-        return self.fc(self.run_segments(x, self._next, "pool"))
+        return self.fc(self.run_units(x, self._cut + 1, self._last))
 
     def forward(self, x):
         return self.stage1(hop(self.stage0(x.to(self.dev0)), self.dev1))

@@ -108,6 +108,43 @@ def test_graphed_pipeline_resnet50_matches_eager():
         _lib.set_deterministic(was)
 
 
+def test_block_level_split_and_time_balanced_cut():
+    """A cut between two bottleneck blocks computes what the unsplit network computes (bit-identical in
+    deterministic mode), and ``balanced()`` picks the cut that minimises the slower stage's measured time."""
+    from pytorch_distributed_training_tutorials_b200 import _lib
+    from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    from pytorch_distributed_training_tutorials_b200.parallel.place import balanced_cuts
+    devs = _devs()
+    was = _lib.is_deterministic()
+    _lib.set_deterministic(True)
+    try:
+        torch.manual_seed(0)
+        whole = resnet50(num_classes=16).to(devs[0])
+        sp = ModelParallelResNet50(num_classes=16, dev0=devs[0], dev1=devs[1], split_after="layer2.1")
+        sp.load_state_dict(whole.state_dict())
+        assert sp.layer2[1].conv1.weight.device == torch.device(devs[0])
+        assert sp.layer2[2].conv1.weight.device == torch.device(devs[1])
+        x = torch.randn(8, 3, 96, 96, device=devs[0]); y = torch.randint(0, 16, (8,), device=devs[0])
+        la = Fn.cross_entropy(whole(x), y); la.backward()
+        lb = Fn.cross_entropy(sp(x), y.to(devs[1])); lb.backward()
+        assert float(la) == float(lb)
+        for (n, p), q in zip(whole.named_parameters(), sp.parameters()):
+            assert torch.equal(p.grad.cpu(), q.grad.cpu()), n
+    finally:
+        _lib.set_deterministic(was)
+    bal = ModelParallelResNet50.balanced(torch.randn(16, 3, 96, 96), chunks=2, reps=2, num_classes=16,
+                                         dev0=devs[0], dev1=devs[1])
+    names = bal.unit_names()
+    times = [bal.unit_times_ms[n] for n in names]
+    assert all(t > 0 for t in times)
+    cut = min(balanced_cuts(times, 2)[0], len(names) - 2)
+    assert bal.split_after == names[cut]
+    out = bal(torch.randn(4, 3, 96, 96, device=devs[0]))
+    assert out.shape == (4, 16) and out.device == torch.device(devs[1])
+
+
 def test_device_prefetcher_hands_out_the_right_batches():
     from pytorch_distributed_training_tutorials_b200.data import DevicePrefetcher
     batches = [(torch.full((1 << 20,), float(i)).pin_memory(), torch.tensor([i]).pin_memory()) for i in range(7)]

@@ -197,6 +197,34 @@ def test_split_resnet_has_reference_param_count():
     assert model_size(resnet50(num_classes=1000)) == 25557032          # 03.model_parallel.ipynb:857,888
 
 
+def test_block_level_units_and_time_balanced_cuts():
+    """Pipeline cuts may fall between any two bottleneck blocks; the cut finder minimises the slowest stage."""
+    from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50
+    from pytorch_distributed_training_tutorials_b200.parallel.place import balanced_cuts
+    m = resnet50(num_classes=10)
+    names = m.unit_names()
+    assert names[0] == "stem" and names[-1] == "pool" and len(names) == 18
+    assert m.unit_index("layer2") == names.index("layer2.3") and m.unit_index("layer2", last=False) == names.index("layer2.0")
+    with pytest.raises(ValueError):
+        m.unit_index("layer9")
+    # every parameter belongs to exactly one unit (fc travels with the pool)
+    owned = sum(sum(p.numel() for mod in m.unit_modules(n) for p in mod.parameters()) for n in names)
+    assert owned + sum(p.numel() for p in m.fc.parameters()) == sum(p.numel() for p in m.parameters())
+    assert balanced_cuts([5, 1, 1, 1, 1, 1], 2) == [0]
+    assert balanced_cuts([1, 1, 1, 1, 1, 5], 2) == [4]
+    assert balanced_cuts([1, 2, 3, 4, 5, 6, 7], 3) == [3, 5]
+    assert balanced_cuts([3.0], 1) == []
+    with pytest.raises(ValueError):
+        balanced_cuts([1, 2], 3)
+    # the split model runs unit-exactly like the unsplit one (both devices the CPU here)
+    torch.manual_seed(0)
+    sp = ModelParallelResNet50(num_classes=10, dev0="cpu", dev1="cpu", split_after="layer2.1")
+    assert sp._cut == names.index("layer2.1")
+    with pytest.raises(ValueError):
+        ModelParallelResNet50(num_classes=10, dev0="cpu", dev1="cpu", split_after="pool")
+
+
 def test_bucket_assignment_matches_torch_resnet50():
     import torchvision
     from pytorch_distributed_training_tutorials_b200.parallel._native_reducer import load
