@@ -15,7 +15,7 @@ from pytorch_distributed_training_tutorials_b200 import _lib
 from pytorch_distributed_training_tutorials_b200.ops import native as NV
 
 dev = torch.device("cuda:0")
-NB = 256
+NB = int(os.environ.get("NCU_NB", "256"))      # batch; NCU_NB=8 exposes the latency floor of a launch
 bf = torch.bfloat16
 
 

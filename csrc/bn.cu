@@ -15,8 +15,9 @@ namespace b200 {
 constexpr int kBnThreads = 256;
 constexpr int kUnroll = 4;
 constexpr int kUnrollBwd = 4;
-// The partial-sum array behind `sums` has b200::bn_replicas() copies: 16 normally (spreads the atomics
-// of ~900 CTAs), one per row-slab CTA in deterministic mode (plain stores, folded in slab order).
+// The partial-sum array behind `sums` has b200::bn_replicas_used(C) copies: up to 16 (spreads the atomics
+// of ~900 CTAs; fewer for wide layers), one per row-slab CTA in deterministic mode (plain stores, folded in
+// slab order), then one ticket word.
 
 struct Slab {
   int cols_per_block;   // vector (8-channel) columns handled by one CTA
@@ -47,8 +48,7 @@ static Slab make_slab(long long rows, int C, int target_blocks) {
 // all threads (no serial tail on a few threads).
 template <int NACC>
 __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int cols, int C,
-                                             float* smem, float* __restrict__ out, int reps, int reps_alloc,
-                                             int det) {
+                                             float* smem, float* __restrict__ out, int reps, int det) {
   constexpr int NV = NACC * 8;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nwarps = kBnThreads / 32;
@@ -76,13 +76,13 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
     else atomicAdd(out + (size_t)(blockIdx.y % reps) * 2 * C + (v >> 3) * C + col * 8 + (v & 7), s);
   }
   // The last CTA to finish folds the replicas into copy 0, so consumers read one plain array.
-  // `reps` = copies in use, `reps_alloc` = copies the buffer holds (the ticket word sits behind those).
+  // `reps` = copies in use (bn_replicas_used(C)); the ticket word sits right behind them.
   if (!det && reps == 1) return;                  // a single copy IS the result
   __shared__ bool is_last;
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    unsigned int* ticket = reinterpret_cast<unsigned int*>(out + (size_t)reps_alloc * 2 * C);
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(out + (size_t)reps * 2 * C);
     is_last = (atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1);
   }
   __syncthreads();
@@ -94,7 +94,7 @@ __device__ __forceinline__ void fold_and_add(float (&acc)[NACC][8], int tx, int 
 
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long rows, int C,
-                int cols, int rowlanes, int reps, int reps_alloc, int det) {
+                int cols, int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
@@ -124,7 +124,7 @@ bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long
       for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] += f[j] * f[j]; }
     }
   }
-  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, reps_alloc, det);
+  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, det);
 }
 
 template <bool kTrain>
@@ -219,7 +219,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                      const float* __restrict__ save_invstd, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ sums,
                      uint4* __restrict__ dres, long long rows, int C, int relu, int cols,
-                     int rowlanes, int reps, int reps_alloc, int det) {
+                     int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
@@ -280,7 +280,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
       }
     }
   }
-  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, reps_alloc, det);
+  fold_and_add<2>(acc, tx, cols, C, smem, sums, reps, det);
 }
 
 template <int kMask>
@@ -353,11 +353,12 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
 
 static int target_blocks() { return 148 * 6; }
 
-// Zero what the reduction adds into.  With a single copy in use there is no ticket and no fold: only that
-// copy is cleared; otherwise everything up to and including the ticket word behind the allocated copies.
-static cudaError_t clear_sums(float* sums, int C, int reps_alloc, int used, cudaStream_t st) {
-  if (used == 1 && !deterministic()) return cudaMemsetAsync(sums, 0, sizeof(float) * (size_t)2 * C, st);
-  return cudaMemsetAsync(sums, 0, sizeof(float) * ((size_t)2 * C * reps_alloc + 1), st);
+// Zero what the reduction adds into: the copies in use and the ticket word behind them -- unless the caller
+// has promised zeroed buffers (b200dt_set_sums_prezeroed; the Python layer carves them from zero-filled chunks,
+// which removes ~160 memset nodes from a ResNet-50 step).
+static cudaError_t clear_sums(float* sums, int C, int used, cudaStream_t st) {
+  if (sums_prezeroed()) return cudaSuccess;
+  return cudaMemsetAsync(sums, 0, sizeof(float) * ((size_t)2 * C * used + 1), st);
 }
 
 }  // namespace b200
@@ -367,13 +368,13 @@ using namespace b200;
 extern "C" int b200dt_bn_stats(const void* x, float* sums, long long rows, int C, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   cudaStream_t st = (cudaStream_t)stream;
-  const int reps = bn_replicas(), used = bn_replicas_used(C);
-  cudaError_t e = clear_sums(sums, C, reps, used, st);
+  const int used = bn_replicas_used(C);
+  cudaError_t e = clear_sums(sums, C, used, st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
   bn_stats_kernel<<<s.grid, kBnThreads, smem, st>>>(reinterpret_cast<const uint4*>(x), sums, rows, C,
-                                                    s.cols_per_block, s.rows_per_iter, used, reps,
+                                                    s.cols_per_block, s.rows_per_iter, used,
                                                     deterministic());
   return (int)cudaGetLastError();
 }
@@ -414,8 +415,8 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
   if (relu && y == nullptr && (gamma == nullptr || beta == nullptr)) return -3;
   if (relu == 2 && (y == nullptr || dres == nullptr)) return -3;   // bit-mask mode materialises the masked gradient
   cudaStream_t st = (cudaStream_t)stream;
-  const int reps = bn_replicas(), used = bn_replicas_used(C);
-  cudaError_t e = clear_sums(sums, C, reps, used, st);
+  const int used = bn_replicas_used(C);
+  cudaError_t e = clear_sums(sums, C, used, st);
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
@@ -425,7 +426,7 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
       reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
       reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter, used,      \
-      reps, deterministic())
+      deterministic())
   if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1);
   else if (mask == 2) B200_LAUNCH_REDUCE(2); else B200_LAUNCH_REDUCE(3);
 #undef B200_LAUNCH_REDUCE

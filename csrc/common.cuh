@@ -88,8 +88,9 @@ int deterministic();
 // Copies of the partial-sum array behind a BatchNorm `sums` buffer: B200DT_BN_REPLICAS normally, one
 // per possible CTA slot (B200DT_BN_REPLICAS_DET) in deterministic mode.
 int bn_replicas();
-// copies a C-channel reduction spreads its atomics over (<= bn_replicas(); the ticket word stays behind
-// bn_replicas() copies, which is what callers allocate)
+// copies a C-channel reduction spreads its atomics over (<= bn_replicas()); the ticket word follows them
 int bn_replicas_used(int C);
+// the caller hands in zeroed `sums` buffers (b200dt_set_sums_prezeroed): the entry points skip their memset
+int sums_prezeroed();
 
 }  // namespace b200

@@ -32,8 +32,23 @@ int bn_replicas_used(int C) {
   return r > B200DT_BN_REPLICAS ? B200DT_BN_REPLICAS : r;
 }
 
+static std::atomic<int> g_prezeroed{0};
+int sums_prezeroed() { return g_prezeroed.load(std::memory_order_relaxed); }
+
 }  // namespace b200
 
 extern "C" void b200dt_set_deterministic(int on) { b200::g_det.store(on ? 1 : 0, std::memory_order_relaxed); }
 extern "C" int b200dt_get_deterministic(void) { return b200::deterministic(); }
 extern "C" int b200dt_bn_replicas(void) { return b200::bn_replicas(); }
+extern "C" int b200dt_bn_replicas_used(int C) { return b200::bn_replicas_used(C); }
+extern "C" void b200dt_set_sums_prezeroed(int on) { b200::g_prezeroed.store(on ? 1 : 0, std::memory_order_relaxed); }
+extern "C" int b200dt_get_sums_prezeroed(void) { return b200::sums_prezeroed(); }
+extern "C" unsigned long long b200dt_capture_id(void* stream) {
+  cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
+  unsigned long long id = 0;
+  if (cudaStreamGetCaptureInfo((cudaStream_t)stream, &status, &id) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return status == cudaStreamCaptureStatusActive ? id : 0;
+}

@@ -77,8 +77,9 @@ struct GemmParams {
   const float* bias;
   // deterministic mode (b200::deterministic()): sums are combined in a fixed order
   int det;                  // 1: no floating-point atomics anywhere in this launch
-  int bn_reps;              // copies of {sum, sumsq}[bn_C] behind bn_sums (ticket word follows them)
-  int bn_used;              // copies the atomics are spread over (<= bn_reps; 1: no ticket, no fold)
+  int bn_reps;              // deterministic mode: CTA slots behind bn_sums
+  int bn_used;              // copies of {sum, sumsq}[bn_C] the atomics are spread over (ticket word follows them;
+                            // 1 outside deterministic mode: no ticket, no fold)
   long long split_stride;   // WGRAD, det: split s writes its partial tile to C + s * split_stride
 };
 
@@ -630,7 +631,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       asm volatile("bar.sync 2, 256;" ::: "memory");
       uint32_t mine = 0, fold_last = 0;
       if (threadIdx.x == 64) {
-        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.bn_sums + (size_t)p.bn_reps * 2 * p.bn_C);
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.bn_sums + (size_t)p.bn_used * 2 * p.bn_C);
         mine = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
       }
       // broadcast the verdict through the barrier's OR-reduction (no static shared memory: the
@@ -902,10 +903,8 @@ using namespace b200;
 
 // C[M,N] (bf16 or fp32) = A[M,K] * B[N,K]^T (+ bias[N]) (ReLU)     -- all row-major, bf16 inputs.
 static int clear_bn_sums(float* bn_sums, int C, cudaStream_t st) {
-  if (bn_sums == nullptr) return 0;
-  if (!deterministic() && bn_replicas_used(C) == 1)       // one copy, no ticket (see the fold in the kernel)
-    return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * (size_t)2 * C, st);
-  return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * bn_replicas() + 1), st);
+  if (bn_sums == nullptr || sums_prezeroed()) return 0;
+  return (int)cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * C * bn_replicas_used(C) + 1), st);
 }
 
 extern "C" int b200dt_gemm_tn_bf16(const void* A, const void* B, void* C, int M, int N, int K,

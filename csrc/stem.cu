@@ -477,9 +477,10 @@ extern "C" int b200dt_stem_conv_fprop(const float* x, const float* w, void* y, i
     if (e != cudaSuccess) return (int)e;
     configured[dev] = true;
   }
-  const int det = deterministic(), reps = bn_replicas();
+  const int det = deterministic(), reps = bn_replicas_used(64);
   if (bn_sums != nullptr) {
-    cudaError_t e = cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * 64 * reps + 1), st);
+    cudaError_t e = sums_prezeroed() ? cudaSuccess
+                                     : cudaMemsetAsync(bn_sums, 0, sizeof(float) * ((size_t)2 * 64 * reps + 1), st);
     if (e != cudaSuccess) return (int)e;
   }
   const int ntiles = NB * ((W / 2) / kStemTW) * ((H / 2) / kFwdRows);

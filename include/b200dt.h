@@ -71,10 +71,20 @@ int b200dt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int NB, int C, int H, 
  * Replaces cuDNN BatchNorm + ATen relu/add in torchvision Bottleneck (03.model_parallel.ipynb:810).
  * csrc/bn.cu.  x, y, residual, dy, dx, dres: [rows, C] bf16 (NHWC flattened); C % 8 == 0. */
 
-/* `sums` holds B200DT_BN_REPLICAS copies of {sum x [C], sum x^2 [C]} (fp32; cleared by the call; CTAs
- * spread their atomics over the copies and the last CTA folds them into copy 0, which is what the
- * apply kernels read) followed by one ticket word: 2*C*B200DT_BN_REPLICAS + 1 floats. */
+/* `sums` holds b200dt_bn_replicas_used(C) copies of {sum x [C], sum x^2 [C]} (fp32; cleared by the call; CTAs
+ * spread their atomics over the copies and the last CTA folds them into copy 0, which is what the apply
+ * kernels read) followed by one ticket word.  The copy count falls with C (min(16, 2048 / C), at least 1:
+ * wide layers have little contention and the fold costs 2*C*copies loads), so 2*C*B200DT_BN_REPLICAS + 1
+ * floats is always enough; 2*C*b200dt_bn_replicas_used(C) + 1 is exact.
+ * b200dt_set_sums_prezeroed(1): the caller promises that every `sums` / `bn_sums` buffer it passes is already
+ * zero (all copies and the ticket word), and the entry points stop issuing their own memset -- a process-wide
+ * switch for callers that carve the buffers from zero-filled memory (ops/native.py does: ~160 memset nodes
+ * less per ResNet-50 step).  b200dt_capture_id: id of the stream capture `stream` is in, 0 if none. */
 #define B200DT_BN_REPLICAS 16
+int b200dt_bn_replicas_used(int C);
+void b200dt_set_sums_prezeroed(int on);
+int b200dt_get_sums_prezeroed(void);
+unsigned long long b200dt_capture_id(void* stream);
 /* Deterministic mode (env B200DT_DETERMINISTIC=1 or b200dt_set_deterministic(1); no counterpart call in
  * the reference, it is a regression-testing aid): every fp32 sum that is otherwise combined with atomics
  * (BatchNorm statistics, BatchNorm-backward partials, split-K weight gradients, bias gradients, the SIMT

@@ -136,6 +136,14 @@ def lib() -> "_Counted":
         handle.b200dt_get_deterministic.argtypes = []
         handle.b200dt_bn_replicas.restype = i32
         handle.b200dt_bn_replicas.argtypes = []
+        handle.b200dt_bn_replicas_used.restype = i32
+        handle.b200dt_bn_replicas_used.argtypes = [i32]
+        handle.b200dt_set_sums_prezeroed.restype = None
+        handle.b200dt_set_sums_prezeroed.argtypes = [i32]
+        handle.b200dt_get_sums_prezeroed.restype = i32
+        handle.b200dt_get_sums_prezeroed.argtypes = []
+        handle.b200dt_capture_id.restype = C.c_ulonglong
+        handle.b200dt_capture_id.argtypes = [C.c_void_p]
         handle.b200dt_version.restype = C.c_char_p
         handle.b200dt_error_string.restype = C.c_char_p
         handle.b200dt_error_string.argtypes = [i32]

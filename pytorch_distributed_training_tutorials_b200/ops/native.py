@@ -17,8 +17,46 @@ F32 = torch.float32
 
 
 def bn_replicas() -> int:
-    """Copies of the partial-sum array behind a BatchNorm ``sums`` buffer (16; 160 in deterministic mode)."""
+    """Upper bound on the copies of the partial-sum array behind a BatchNorm ``sums`` buffer (16; 160 in
+    deterministic mode); ``bn_replicas_used(C)`` is the exact count for a C-channel layer."""
     return int(lib().b200dt_bn_replicas())
+
+
+def bn_replicas_used(C: int) -> int:
+    return int(lib().b200dt_bn_replicas_used(int(C)))
+
+
+# Zero-filled scratch for the statistics kernels.  Every conv-with-statistics, bn_stats and bn_bwd_reduce launch
+# needs its partial-sum copies and ticket word zeroed first; as a memset per launch that is ~160 extra nodes in a
+# ResNet-50 step (~3 us each when replayed from a graph).  Instead the buffers are carved, once each, from chunks
+# that ONE fill zeroes, and the library is told not to memset (b200dt_set_sums_prezeroed).  A chunk belongs to one
+# (device, stream, stream-capture) triple: the fill is ordered before every kernel that uses a slice, and a
+# captured graph re-runs its own fill on every replay.
+_ZERO_CHUNK_FLOATS = 1 << 20
+_zero_chunks: dict = {}
+
+
+def zeroed_floats(n: int, device) -> torch.Tensor:
+    """``n`` fp32 zeros on ``device`` (256-byte aligned), valid for ONE accumulate-into use on the current stream."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        return torch.zeros(n, device=device, dtype=F32)
+    L = lib()
+    if not L.b200dt_get_sums_prezeroed():
+        L.b200dt_set_sums_prezeroed(1)
+    n64 = (int(n) + 63) // 64 * 64
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    st = torch.cuda.current_stream(idx).cuda_stream
+    cap = int(L.b200dt_capture_id(st))
+    key = (idx, st)
+    ent = _zero_chunks.get(key)
+    if ent is None or ent[2] != cap or ent[1] + n64 > ent[0].numel():
+        with torch.cuda.device(idx):
+            ent = [torch.zeros(max(_ZERO_CHUNK_FLOATS, n64), device=device, dtype=F32), 0, cap]
+        _zero_chunks[key] = ent
+    out = ent[0][ent[1]:ent[1] + n]
+    ent[1] += n64
+    return out
 
 
 def _need(t: torch.Tensor, dtype, name: str) -> None:
@@ -29,8 +67,9 @@ def _need(t: torch.Tensor, dtype, name: str) -> None:
 
 # --------------------------------------------------------------------------- GEMM / conv
 def bn_sums_buffer(C: int, device) -> torch.Tensor:
-    """Scratch for BatchNorm statistics: replicated {sum, sum of squares} + ticket (see bn.cu)."""
-    return torch.empty(2 * C * bn_replicas() + 1, device=device, dtype=F32)
+    """Scratch for BatchNorm statistics: replicated {sum, sum of squares} + ticket (see bn.cu), zeroed.
+    Good for ONE launch: the kernels add into it and do not clear it (``zeroed_floats``)."""
+    return zeroed_floats(2 * C * bn_replicas_used(C) + 1, device)
 
 
 def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
@@ -270,7 +309,7 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------- batch norm
 def bn_stats(x2d: torch.Tensor) -> torch.Tensor:
     rows, Cc = x2d.shape
-    sums = torch.empty(2 * Cc * bn_replicas() + 1, device=x2d.device, dtype=F32)
+    sums = bn_sums_buffer(Cc, x2d.device)
     with on_device(x2d.device):
         check(lib().b200dt_bn_stats(ptr(x2d), ptr(sums), rows, Cc, stream_ptr(x2d.device)), "bn_stats")
     return sums
@@ -319,7 +358,7 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
     if relu and relu_mask is not None:
         dres = torch.empty_like(dy2d)
         dx = torch.empty_like(x2d)
-        sums = torch.empty(2 * Cc * bn_replicas() + 1, device=dev, dtype=F32)
+        sums = bn_sums_buffer(Cc, dev)
         dgamma = torch.empty(Cc, device=dev, dtype=F32)
         dbeta = torch.empty(Cc, device=dev, dtype=F32)
         with on_device(dev):
@@ -331,7 +370,7 @@ def bn_backward(dy2d, y2d, x2d, save_mean, save_invstd, gamma, relu: bool, want_
                                             ptr(gamma), ptr(beta), ptr(sums), ptr(dx), ptr(dgamma), ptr(dbeta),
                                             rows, Cc, 0, st), "bn_bwd_apply")
         return dx, dgamma, dbeta, (dres if want_dres else None)
-    sums = torch.empty(2 * Cc * bn_replicas() + 1, device=dev, dtype=F32)
+    sums = bn_sums_buffer(Cc, dev)
     dres = torch.empty_like(dy2d) if want_dres else None
     dx = torch.empty_like(x2d)
     dgamma = torch.empty(Cc, device=dev, dtype=F32)

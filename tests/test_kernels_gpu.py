@@ -419,7 +419,6 @@ def test_implicit_gemm_stem_matches_fp32_conv(nb, hw):
     w = torch.randn(64, 7, 7, 3, device=dev) * 0.1
     assert NV.stem_supported(x.shape)
     sums = NV.bn_sums_buffer(64, dev)
-    sums.fill_(float("nan"))
     y = NV.stem_conv_fprop(x, w, bn_sums=sums)
     xb, wb = x.bfloat16().float(), w.bfloat16().float()
     ref = torch.nn.functional.conv2d(xb, wb.permute(0, 3, 1, 2), stride=2, padding=3).permute(0, 2, 3, 1)
@@ -437,6 +436,47 @@ def test_implicit_gemm_stem_matches_fp32_conv(nb, hw):
     assert ((dw - ref_dw).norm() / ref_dw.norm()).item() < 5e-3
 
 
+@pytest.mark.parametrize("C", [64, 256, 1024, 2048])
+def test_sums_buffers_zero_chunks_and_the_memset_contract(C):
+    """Statistics buffers are slices of zero-filled chunks (one fill instead of a memset per launch) and the
+    library is told not to clear them; with the switch off (the C ABI's default) the entry points clear any
+    buffer themselves.  Wide layers use fewer partial-sum copies (and 2048 channels none to fold)."""
+    from pytorch_distributed_training_tutorials_b200 import _lib
+    from pytorch_distributed_training_tutorials_b200.ops import native as NV
+    dev = torch.device("cuda:0")
+    L = _lib.lib()
+    used = NV.bn_replicas_used(C)
+    assert used == (NV.bn_replicas() if _lib.is_deterministic() else max(1, min(16, 2048 // C)))
+    torch.manual_seed(C)
+    x = torch.randn(777, C, device=dev).to(torch.bfloat16)
+    xf = x.float()
+    ref = torch.cat([xf.sum(0), (xf * xf).sum(0)])
+    a = NV.bn_stats(x)
+    b = NV.bn_stats(x)
+    assert L.b200dt_get_sums_prezeroed() == 1
+    assert a.data_ptr() != b.data_ptr() and a.data_ptr() % 256 == 0 and b.data_ptr() % 256 == 0
+    assert torch.allclose(a[:2 * C], ref, rtol=1e-4, atol=1e-2) and torch.allclose(b[:2 * C], ref, rtol=1e-4, atol=1e-2)
+    # inside a stream capture the chunk (and its fill) belong to the graph: replays start from zeros again
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.graph(g, stream=s):
+        c = NV.bn_stats(x)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.allclose(c[:2 * C], ref, rtol=1e-4, atol=1e-2)
+    # the C ABI default: a dirty caller-owned buffer is cleared by the call
+    L.b200dt_set_sums_prezeroed(0)
+    try:
+        dirty = torch.full((2 * C * NV.bn_replicas() + 1,), float("nan"), device=dev)
+        rc = L.b200dt_bn_stats(x.data_ptr(), dirty.data_ptr(), 777, C, torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+        assert torch.allclose(dirty[:2 * C], ref, rtol=1e-4, atol=1e-2)
+    finally:
+        L.b200dt_set_sums_prezeroed(1)
+
+
 @pytest.mark.parametrize("nb,H", [(3, 56), (2, 28), (5, 12), (1, 16), (2, 7)])
 def test_halo_reuse_3x3_64_to_64(nb, H):
     """3x3 / stride 1 / 64 -> 64 runs in halo mode (one staged patch, nine shifted operand views, resident filter).
@@ -449,7 +489,6 @@ def test_halo_reuse_3x3_64_to_64(nb, H):
     w = (torch.randn(64, 3, 3, 64, device=dev) * 0.06).to(torch.bfloat16)
     dy = torch.randn(nb, H, H, 64, device=dev).to(torch.bfloat16)
     sums = NV.bn_sums_buffer(64, dev)
-    sums.fill_(float("nan"))
     y = NV.conv2d_fprop(x, w, bn_sums=sums)
     xf, wf = x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2)
     ref = torch.nn.functional.conv2d(xf, wf, padding=1).permute(0, 2, 3, 1)
