@@ -226,7 +226,9 @@ def run_reference(args, rank, world, local):
                               "scripts without setup.py/pyproject, pip cannot install it and no copy was shipped"}))
             return None
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29611")
+    if "MASTER_PORT" not in os.environ:           # single process without a launcher: any free port
+        from pytorch_distributed_training_tutorials_b200.group import find_free_port
+        os.environ["MASTER_PORT"] = str(find_free_port()) if world == 1 else "29611"
     os.environ.setdefault("RANK", str(rank)); os.environ.setdefault("WORLD_SIZE", str(world))
     os.environ.setdefault("LOCAL_RANK", str(local))
     sys.path.insert(0, ref_dir)

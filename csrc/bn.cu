@@ -96,6 +96,8 @@ __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long rows, int C,
                 int cols, int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
+  griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
@@ -136,6 +138,8 @@ bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint
                 const float* __restrict__ in_var, long long rows, int C, float eps, float momentum,
                 int relu, int cols, int rowlanes, long long* batches_tracked,
                 unsigned char* __restrict__ relu_mask) {
+  griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
@@ -221,6 +225,8 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                      uint4* __restrict__ dres, long long rows, int C, int relu, int cols,
                      int rowlanes, int reps, int det) {
   extern __shared__ float smem[];
+  griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
@@ -291,6 +297,8 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                     const float* __restrict__ beta, const float* __restrict__ sums,
                     uint4* __restrict__ dx, float* dgamma, float* dbeta, long long rows, int C,
                     int relu, int cols, int rowlanes) {
+  griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8;
   const int tx = threadIdx.x % cols, ty = threadIdx.x / cols;
   const int col = blockIdx.x * cols + tx;
@@ -373,10 +381,9 @@ extern "C" int b200dt_bn_stats(const void* x, float* sums, long long rows, int C
   if (e != cudaSuccess) return (int)e;
   Slab s = make_slab(rows, C, target_blocks());
   const size_t smem = sizeof(float) * kBnThreads * 16;
-  bn_stats_kernel<<<s.grid, kBnThreads, smem, st>>>(reinterpret_cast<const uint4*>(x), sums, rows, C,
-                                                    s.cols_per_block, s.rows_per_iter, used,
-                                                    deterministic());
-  return (int)cudaGetLastError();
+  e = launch_pdl(kPdlBn, bn_stats_kernel, s.grid, dim3(kBnThreads), smem, st, reinterpret_cast<const uint4*>(x), sums,
+                 rows, C, s.cols_per_block, s.rows_per_iter, used, deterministic());
+  return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 extern "C" int b200dt_bn_apply(const void* x, const void* residual, void* y, const float* sums,
@@ -386,12 +393,13 @@ extern "C" int b200dt_bn_apply(const void* x, const void* residual, void* y, con
                                long long* batches_tracked, unsigned char* relu_mask, void* stream) {
   if (C % 8 || rows <= 0) return -3;
   Slab s = make_slab(rows, C, target_blocks());
-  bn_apply_kernel<true><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
+  cudaError_t e = launch_pdl(
+      kPdlBn, bn_apply_kernel<true>, s.grid, dim3(kBnThreads), 0, (cudaStream_t)stream,
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), sums, gamma, beta, running_mean, running_var, save_mean,
       save_invstd, nullptr, nullptr, rows, C, eps, momentum, relu, s.cols_per_block,
       s.rows_per_iter, batches_tracked, relu ? relu_mask : nullptr);
-  return (int)cudaGetLastError();
+  return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y,
@@ -400,11 +408,12 @@ extern "C" int b200dt_bn_apply_eval(const void* x, const void* residual, void* y
                                     void* stream) {
   if (C % 8 || rows <= 0) return -3;
   Slab s = make_slab(rows, C, target_blocks());
-  bn_apply_kernel<false><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(
+  cudaError_t e = launch_pdl(
+      kPdlBn, bn_apply_kernel<false>, s.grid, dim3(kBnThreads), 0, (cudaStream_t)stream,
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual),
       reinterpret_cast<uint4*>(y), nullptr, gamma, beta, nullptr, nullptr, nullptr, nullptr, mean,
       var, rows, C, eps, 0.f, relu, s.cols_per_block, s.rows_per_iter, nullptr, nullptr);
-  return (int)cudaGetLastError();
+  return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x,
@@ -422,7 +431,7 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
   const size_t smem = sizeof(float) * kBnThreads * 16;
   const int mask = !relu ? 0 : (relu == 2 ? 3 : (y != nullptr ? 1 : 2));
 #define B200_LAUNCH_REDUCE(M)                                                                      \
-  bn_bwd_reduce_kernel<M><<<s.grid, kBnThreads, smem, st>>>(                                       \
+  e = launch_pdl(kPdlBn, bn_bwd_reduce_kernel<M>, s.grid, dim3(kBnThreads), smem, st,                      \
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
       reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
       reinterpret_cast<uint4*>(dres), rows, C, relu, s.cols_per_block, s.rows_per_iter, used,      \
@@ -430,7 +439,7 @@ extern "C" int b200dt_bn_bwd_reduce(const void* dy, const void* y, const void* x
   if (mask == 0) B200_LAUNCH_REDUCE(0); else if (mask == 1) B200_LAUNCH_REDUCE(1);
   else if (mask == 2) B200_LAUNCH_REDUCE(2); else B200_LAUNCH_REDUCE(3);
 #undef B200_LAUNCH_REDUCE
-  return (int)cudaGetLastError();
+  return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 extern "C" int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x,
@@ -443,11 +452,12 @@ extern "C" int b200dt_bn_bwd_apply(const void* dy, const void* y, const void* x,
   Slab s = make_slab(rows, C, target_blocks());
   const int mask = !relu ? 0 : (y != nullptr ? 1 : 2);
 #define B200_LAUNCH_APPLY(M)                                                                       \
-  bn_bwd_apply_kernel<M><<<s.grid, kBnThreads, 0, (cudaStream_t)stream>>>(                         \
+  e = launch_pdl(kPdlBn, bn_bwd_apply_kernel<M>, s.grid, dim3(kBnThreads), 0, (cudaStream_t)stream,        \
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),                       \
       reinterpret_cast<const uint4*>(x), save_mean, save_invstd, gamma, beta, sums,                \
       reinterpret_cast<uint4*>(dx), dgamma, dbeta, rows, C, relu, s.cols_per_block, s.rows_per_iter)
+  cudaError_t e = cudaSuccess;
   if (mask == 0) B200_LAUNCH_APPLY(0); else if (mask == 1) B200_LAUNCH_APPLY(1); else B200_LAUNCH_APPLY(2);
 #undef B200_LAUNCH_APPLY
-  return (int)cudaGetLastError();
+  return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }

@@ -93,4 +93,31 @@ int bn_replicas_used(int C);
 // the caller hands in zeroed `sums` buffers (b200dt_set_sums_prezeroed): the entry points skip their memset
 int sums_prezeroed();
 
+// kernels launched through launch_pdl may begin (prologue only: they call griddep_wait() before touching memory)
+// while the previous kernel of the stream drains.  B200DT_PDL is a mask over kernel classes (kPdlGemm,
+// kPdlBn); 0 turns the attribute off everywhere.
+int pdl_enabled();
+constexpr int kPdlGemm = 1, kPdlBn = 2;
+
+// Launch with programmatic stream serialization: the kernel's CTAs may become resident while the tail of the
+// previous kernel in the stream is still running, and sit in griddepcontrol.wait until that kernel has completed.
+// Hides launch latency and the prologue (barrier init, TMEM allocation, descriptor prefetch) of the ~340 short
+// kernels of a ResNet-50 step; captured into CUDA graphs as programmatic edges.  The kernel MUST execute
+// griddep_wait() in every thread before its first global-memory access.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int cls, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = (pdl_enabled() & cls) ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace b200

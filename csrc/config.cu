@@ -32,6 +32,17 @@ int bn_replicas_used(int C) {
   return r > B200DT_BN_REPLICAS ? B200DT_BN_REPLICAS : r;
 }
 
+static std::atomic<int> g_pdl{-1};
+int pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200DT_PDL");
+    v = (e != nullptr && e[0] != '\0') ? atoi(e) : 1;
+    g_pdl.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
 static std::atomic<int> g_prezeroed{0};
 int sums_prezeroed() { return g_prezeroed.load(std::memory_order_relaxed); }
 

@@ -200,6 +200,9 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   if (warp == 1) {
     tmem_alloc<512>(&bars->tmem_base);
   }
+  // everything above touched only parameters, shared memory and TMEM: it may overlap the previous kernel's tail
+  griddep_launch_dependents();
+  griddep_wait();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -791,7 +794,8 @@ static int launch(const CUtensorMap mapsA[kMaxMaps], const CUtensorMap mapsB[kMa
   TmaMaps maps;
   for (int i = 0; i < kMaxMaps; ++i) { maps.a[i] = mapsA[i]; maps.b[i] = mapsB[i]; }
   maps.c = mapC != nullptr ? *mapC : mapsA[0];
-  tc_gemm_kernel<<<grid, kThreads, smem, stream>>>(maps, p);
+  cudaError_t le = launch_pdl(kPdlGemm, tc_gemm_kernel, dim3(grid), dim3(kThreads), (size_t)smem, stream, maps, p);
+  if (le != cudaSuccess) return (int)le;
   return (int)cudaGetLastError();
 }
 

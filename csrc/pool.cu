@@ -23,19 +23,30 @@ maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, uint2* __
     uint32_t arg[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+    // all nine loads are issued before the first compare: out-of-range taps read a clamped (valid) address
+    // and are discarded afterwards, so no load sits behind a branch
+    uint4 v[9];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = min(max(ho * 2 - 1 + r, 0), H - 1);
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = min(max(wo * 2 - 1 + s, 0), W - 1);
+        v[r * 3 + s] = ld_nc_v4(x + (((long long)n * H + h) * W + w) * cv + c);
+      }
+    }
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int h = ho * 2 - 1 + r;
-      if (h < 0 || h >= H) continue;
 #pragma unroll
       for (int s = 0; s < 3; ++s) {
         const int w = wo * 2 - 1 + s;
-        if (w < 0 || w >= W) continue;
+        const bool inside = h >= 0 && h < H && w >= 0 && w < W;
         float f[8];
-        unpack8(ld_nc_v4(x + (((long long)n * H + h) * W + w) * cv + c), f);
+        unpack8(v[r * 3 + s], f);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (f[j] > best[j]) { best[j] = f[j]; arg[j] = r * 3 + s; }
+          if (inside && f[j] > best[j]) { best[j] = f[j]; arg[j] = r * 3 + s; }
       }
     }
     y[i] = pack8(best);
@@ -68,16 +79,26 @@ maxpool_bwd_kernel(const uint4* __restrict__ dy, const uint2* __restrict__ argma
       for (int j = 0; j < 8; ++j) g[q][j] = 0.f;
     // window (k + a, l + b) reaches patch pixel q = 2*py + px with arg-max code kCode[a][b][q]
     // (code = r*3 + s of the window element; 255 = the window does not cover that pixel)
+    // the four (arg-max, dy) pairs are loaded up front from clamped (always valid) addresses; windows that do
+    // not exist contribute nothing
+    uint2 amv[4];
+    uint4 dyv[4];
 #pragma unroll
-    for (int a = 0; a < 2; ++a) {
-      if (k + a >= Ho) continue;
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
-        if (l + b >= Wo) continue;
-        const long long o = (((long long)n * Ho + (k + a)) * Wo + (l + b)) * cv + c;
-        const uint2 am = argmax[o];
+        const long long o = (((long long)n * Ho + min(k + a, Ho - 1)) * Wo + min(l + b, Wo - 1)) * cv + c;
+        amv[a * 2 + b] = argmax[o];
+        dyv[a * 2 + b] = ld_nc_v4(dy + o);
+      }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const bool exists = (k + a < Ho) && (l + b < Wo);
+        const uint2 am = amv[a * 2 + b];
         float d[8];
-        unpack8(ld_nc_v4(dy + o), d);
+        unpack8(dyv[a * 2 + b], d);
 #pragma unroll
         for (int py = 0; py < 2; ++py) {
           const int r = 2 * (0 - a) + py + 1;          // row of the pixel inside window k + a
@@ -90,7 +111,7 @@ maxpool_bwd_kernel(const uint4* __restrict__ dy, const uint2* __restrict__ argma
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const uint32_t aj = ((j < 4 ? am.x : am.y) >> ((j & 3) * 8)) & 0xff;
-              if (aj == code) g[py * 2 + px][j] += d[j];
+              if (exists && aj == code) g[py * 2 + px][j] += d[j];
             }
           }
         }

@@ -284,4 +284,11 @@ __device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
                : "memory");
 }
 
+// Programmatic dependent launch (csrc/common.cuh: launch_pdl).  launch_dependents: the next kernel in the stream
+// may start launching its CTAs once every CTA of this grid has got here or exited; wait: block until every grid
+// this launch depends on has completed and its memory is visible.  Both are no-ops in a kernel that was not
+// launched with the programmatic-serialization attribute.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 }  // namespace b200

@@ -434,14 +434,27 @@ stem_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__
   }
 }
 
-// dw[co][k] = sum over CTAs (in CTA order) of partial[cta][k][co]
-__global__ void stem_wgrad_fold_kernel(const float* __restrict__ partial, float* __restrict__ dw, int nparts) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;       // output index co * 147 + k
-  if (i >= 64 * kStemK) return;
-  const int co = i / kStemK, k = i % kStemK;
+// dw[co][k] = sum over CTAs of partial[cta][k][co], in a fixed order: one block per k, thread (slice, co) adds
+// every fourth partial (coalesced 256-byte rows, eight loads in flight), the four slices are added in slice order.
+__global__ void __launch_bounds__(256)
+stem_wgrad_fold_kernel(const float* __restrict__ partial, float* __restrict__ dw, int nparts) {
+  __shared__ float red[4][64];
+  const int k = blockIdx.x, co = threadIdx.x & 63, slice = threadIdx.x >> 6;
+  const float* src = partial + (size_t)k * 64 + co;
+  constexpr size_t kPart = (size_t)kStemK * 64;
   float acc = 0.f;
-  for (int c = 0; c < nparts; ++c) acc += partial[(size_t)c * (kStemK * 64) + k * 64 + co];
-  dw[i] = acc;
+  int c = slice;
+  for (; c + 28 < nparts; c += 32) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = src[(size_t)(c + 4 * u) * kPart];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += v[u];
+  }
+  for (; c < nparts; c += 4) acc += src[(size_t)c * kPart];
+  red[slice][co] = acc;
+  __syncthreads();
+  if (slice == 0) dw[co * kStemK + k] = ((red[0][co] + red[1][co]) + red[2][co]) + red[3][co];
 }
 
 }  // namespace b200
@@ -512,6 +525,6 @@ extern "C" int b200dt_stem_conv_wgrad(const float* x, const void* dy, float* dw,
   const int grid = stem_grid(nblocks, 0);
   stem_wgrad_kernel<<<grid, kStemThreads, kWgSmem, st>>>(x, reinterpret_cast<const __nv_bfloat16*>(dy), scratch,
                                                         NB, H, W);
-  stem_wgrad_fold_kernel<<<(64 * kStemK + 255) / 256, 256, 0, st>>>(scratch, dw, grid);
+  stem_wgrad_fold_kernel<<<kStemK, 256, 0, st>>>(scratch, dw, grid);
   return (int)cudaGetLastError();
 }

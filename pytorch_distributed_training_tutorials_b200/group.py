@@ -67,9 +67,11 @@ def init(backend: Optional[str] = None, rank: Optional[int] = None, world_size: 
         rank = int(os.environ.get("RANK", "0"))
     if world_size is None:
         world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    auto_port = False
     if "MASTER_PORT" not in os.environ:
         if world_size == 1:
             os.environ["MASTER_PORT"] = str(find_free_port())
+            auto_port = True
         else:
             raise RuntimeError("MASTER_PORT is not set (use the launcher or pass master_port=)")
     if local_rank is None:
@@ -85,8 +87,16 @@ def init(backend: Optional[str] = None, rank: Optional[int] = None, world_size: 
     kwargs = {}
     if backend == "nccl":
         kwargs["device_id"] = device
-    dist.init_process_group(backend=backend, rank=rank, world_size=world_size,
-                            timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
+    for attempt in range(4):
+        try:
+            dist.init_process_group(backend=backend, rank=rank, world_size=world_size,
+                                    timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
+            break
+        except Exception as e:          # noqa: BLE001 -- c10d raises DistNetworkError / RuntimeError by version
+            # a port this process picked itself can be taken between the probe and the bind: pick another one
+            if not auto_port or attempt == 3 or "address already in use" not in str(e).lower():
+                raise
+            os.environ["MASTER_PORT"] = str(find_free_port())
     _state = GroupState(backend=backend, rank=rank, world_size=world_size, local_rank=local_rank,
                         device=device)
     return _state
