@@ -58,7 +58,10 @@ def sweeps():
            "no copy-in / copy-out, the reduce phase alone.",
            "NVLink roofline: 770 GB/s measured peer copy per direction per GPU (B200_PROFILING.md); the multicast (NVLS) path",
            "could not be exercised: torch's symmetric memory reports no multicast support on these boxes.", ""]
-    for f in sorted(glob.glob(os.path.join(G, "allreduce_sweep_*.json"))):
+    inputs = sorted(glob.glob(os.path.join(G, "allreduce_sweep_*.json")))
+    if not inputs:
+        return                                   # keep the committed sweep: nothing newer to build it from
+    for f in inputs:
         d = json.load(open(f)); n = d["world"]; fac = 2 * (n - 1) / n
         keys = [k for k in ("nccl_ms", "oneshot_ms", "twoshot_ms", "nvls_ms", "twoshot_inplace_ms", "nvls_inplace_ms",
                             "twoshot_bf16wire_ms", "nvls_bf16wire_ms") if any(k in r for r in d["rows"])]
@@ -72,18 +75,30 @@ def sweeps():
 def benches():
     out = ["# bench.py results (ResNet-50 DDP bf16, synthetic 224x224, per-GPU batch 256)", "",
            "| file | impl | GPUs | img/s (device-timed) | ms/step | e2e img/s | SM MHz (median) | throttle reasons | kernel launches in timed region |", "|---|---|---|---|---|---|---|---|---|"]
+    # rows of earlier runs whose raw files are gone (every gpurun box is fresh) are kept; a new file of the same
+    # name replaces its row
+    rows = {}
+    prev = os.path.join(P, "bench_results.md")
+    if os.path.exists(prev):
+        for l in open(prev):
+            cells = [c.strip() for c in l.strip().strip("|").split("|")]
+            if len(cells) == 9 and cells[0].endswith(".json"):
+                rows[cells[0]] = l.rstrip("\n")
     for f in sorted(glob.glob(os.path.join(G, "scale_*.json")) + glob.glob(os.path.join(G, "bench_*.json"))):
         try:
             line = [l for l in open(f) if l.startswith("{")][-1]; d = json.loads(line)
         except Exception:
             continue
+        if "value" not in d:
+            continue
         c = d.get("clocks") or {}
-        out.append(f"| {os.path.basename(f)} | {d.get('impl')} | {d['n_gpus']} | {d['value']:.0f} | {d['ms_per_step']:.2f} | {d['e2e']['value']:.0f} | {c.get('sm_mhz')} | {c.get('reasons')} | {d.get('gpu_launches')} |")
-    open(os.path.join(P, "bench_results.md"), "w").write("\n".join(out) + "\n")
+        rows[os.path.basename(f)] = (f"| {os.path.basename(f)} | {d.get('impl')} | {d['n_gpus']} | {d['value']:.0f} | {d['ms_per_step']:.2f} | {d['e2e']['value']:.0f} | {c.get('sm_mhz')} | {c.get('reasons')} | {d.get('gpu_launches')} |")
+    out += [rows[k] for k in sorted(rows)]
+    open(prev, "w").write("\n".join(out) + "\n")
 
 
 def misc():
-    for name in ("graphed_pipeline_bench.json", "pipeline_bench.json", "mp_bench.json", "toy_bench_dp_1.json", "toy_bench_dp_2.json", "toy_bench_ddp_2.json", "toy_bench_dp_8.json", "toy_bench_ddp_8.json", "conv_bench.json", "diag_gemm.json"):
+    for name in ("graphed_pipeline_bench.json", "pipeline_bench.json", "mp_bench.json", "toy_bench_dp_1.json", "toy_bench_dp_2.json", "toy_bench_ddp_2.json", "toy_bench_dp_4.json", "toy_bench_dp_8.json", "toy_bench_ddp_8.json", "conv_bench.json", "diag_gemm.json"):
         f = os.path.join(G, name)
         if os.path.exists(f):
             json.dump(json.load(open(f)), open(os.path.join(P, name), "w"), indent=1)
@@ -103,7 +118,9 @@ def misc():
                "`graphed` = every (stage, micro-batch) replayed from CUDA graphs (`parallel/graphed_pipeline.py`).", "",
                "| variant | ms/step | img/s |", "|---|---|---|"]
         for k, v in d.items():
-            if k.endswith("_ms"):
+            if k.endswith("_chosen"):
+                out.append(f"| {k[:-7]}: time-balanced cut chosen after `{v}` | | |")
+            if k.endswith("_ms") and isinstance(v, (int, float)):
                 out.append(f"| {k[:-3]} | {v:.2f} | {d['batch'] / v * 1e3:.0f} |")
         open(os.path.join(P, "pipeline_bench.md"), "w").write("\n".join(out) + "\n")
     for name, title in (("launches_bs32.csv", "batch 32"),):
@@ -136,5 +153,5 @@ def ncu_reports():
     open(os.path.join(P, "ncu_summaries.md"), "w").write("\n".join(out) + "\n")
 
 
-launches(); conv_bench(); sweeps(); benches(); misc(); ncu_reports()
+launches(); conv_bench(); sweeps(); benches(); misc()      # ncu: bench/ncu_summarise.py
 print(sorted(os.listdir(P)))
