@@ -92,28 +92,48 @@ def placement_table(model: nn.Module) -> List[Tuple[int, str, torch.dtype, torch
 
 # --------------------------------------------------------------------------- placement by measured time
 def profile_units(units: Sequence[Callable], x: torch.Tensor, reps: int = 3,
-                  module: Optional[nn.Module] = None) -> List[float]:
-    """Device time (ms) of forward + backward of every unit of a chain, eager, on ``x``'s device: unit ``k``
-    is fed the output of unit ``k-1``.  The best of ``reps`` runs after one warm-up is kept.  Buffers of
-    ``module`` (running statistics) are restored and its gradients dropped afterwards.  Byte budgets place a
-    LLaMA (``auto_place``); a pipeline wants equal TIME per stage, and for a conv net the two differ a lot:
-    ResNet-50's first half holds 6 % of the parameters and takes 70 % of the step."""
+                  module: Optional[nn.Module] = None, graphed: bool = True) -> List[float]:
+    """Device time (ms) of forward + backward of every unit of a chain on ``x``'s device: unit ``k`` is fed the
+    output of unit ``k-1``.  Each unit is captured into a CUDA graph and the best of ``reps`` replays is kept, so
+    the numbers are what a graph-replayed pipeline will see even where eager launches are host-bound (small
+    micro-batches); ``graphed=False`` (or a unit that cannot be captured) times the eager launches instead.
+    Buffers of ``module`` (running statistics) are restored and its gradients dropped afterwards.  Byte budgets
+    place a LLaMA (``auto_place``); a pipeline wants equal TIME per stage, and for a conv net the two differ a
+    lot: ResNet-50's first half holds 6 % of the parameters and takes 70 % of the step."""
     saved = [b.detach().clone() for b in module.buffers()] if module is not None else []
     times: List[float] = []
     cur = x
     with torch.cuda.device(x.device):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        side = torch.cuda.Stream()
         for f in units:
             xin = cur.detach().requires_grad_(cur.is_floating_point())
-            best, g, y = float("inf"), None, None
+            y = f(xin)                                   # eager warm-up: lazy initialisation, output shape
+            g = torch.ones_like(y)
+            y.backward(g)
+            torch.cuda.synchronize()
+            run = None
+            if graphed:
+                try:
+                    xin.grad = None
+                    side.wait_stream(torch.cuda.current_stream())
+                    gph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gph, stream=side):
+                        yg = f(xin)
+                        yg.backward(g)
+                    run = gph.replay
+                except Exception:                        # noqa: BLE001 -- not capturable: time it eagerly
+                    torch.cuda.synchronize()
+                    run = None
+            if run is None:
+                def run(f=f, xin=xin, g=g):
+                    xin.grad = None
+                    f(xin).backward(g)
+            best = float("inf")
             for _ in range(reps + 1):
-                xin.grad = None
                 torch.cuda.synchronize()
                 e0.record()
-                y = f(xin)
-                if g is None:
-                    g = torch.ones_like(y)
-                y.backward(g)
+                run()
                 e1.record()
                 e1.synchronize()
                 if _ > 0:
