@@ -21,8 +21,11 @@ keep = {"tc_gemm_kernel": "tc_gemm_kernel", "coll_kernelILi1ELi8": "coll_twoshot
         "bn_apply_kernelILb1": "bn_apply_train", "multi_opt_kernelILb0": "multi_sgd", "p2p_bcast_kernel": "p2p_broadcast",
         "p2p_reduce_kernel": "p2p_reduce", "mse_static_kernelIf": "mse_static",
         "skinny_fwd_kernel": "skinny_linear_fwd", "relu_bwd_bias_kernel": "relu_bwd_bias",
-        "stem_im2col_kernel": "stem_im2col", "maxpool_bwd_kernel": "maxpool_bwd"}
-pats = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "SYNCS", "LDGMC", "STGMC", "ATOMG", "REDG", "HMMA", "ELECT", "UBLKCP"]
+        "stem_im2col_kernel": "stem_im2col", "maxpool_bwd_kernel": "maxpool_bwd", "maxpool_fwd_kernel": "maxpool_fwd",
+        "stem_fprop_kernel": "stem_fprop_implicit", "stem_wgrad_kernel": "stem_wgrad_implicit",
+        "p2p_multi_copy_kernel": "p2p_multi_copy", "bn_bwd_apply_kernelILi0": "bn_bwd_apply",
+        "multi_opt_kernelILb1": "multi_adam", "splitk_fold_kernel": "splitk_fold", "ce_kernelIfLi1": "cross_entropy"}
+pats = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "SYNCS", "LDGMC", "STGMC", "ATOMG", "REDG", "HMMA", "ELECT", "UBLKCP", "ACQBULK", "PREEXIT"]
 rows = []
 for name, body in funcs.items():
     for key, short in keep.items():
@@ -38,7 +41,8 @@ for name, body in funcs.items():
 md = ["# SASS mnemonics per kernel (cuobjdump -sass of _native/libb200dt.so, sm_100a)", "",
       "`UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,",
       "`UTMALDG` / `UTMASTG` / `UTMAREDG` = TMA load / store / reduce-add, `SYNCS` = mbarrier, `LDGMC` / `STGMC`-class =",
-      "multimem (NVLS), `ATOMG...SYS` = system-scope flag CAS. No `HMMA` (legacy mma.sync) anywhere.", "",
+      "multimem (NVLS), `ATOMG...SYS` = system-scope flag CAS, `ACQBULK` / `PREEXIT` = griddepcontrol.wait / .launch_dependents",
+      "(programmatic dependent launch). No `HMMA` (legacy mma.sync) anywhere.", "",
       "| kernel | instructions | " + " | ".join(pats) + " |", "|---|---|" + "---|" * len(pats)]
 for name, n, cnt in sorted(rows, key=lambda r: -r[1]):
     md.append(f"| `{name[:70]}` | {n} | " + " | ".join(str(cnt.get(p, 0) or "") for p in pats) + " |")
