@@ -6,6 +6,9 @@
 it sees).  On 4 GPUs every ``[32, 32]`` batch shows up as 4 x ``[8, 32]`` inside the replicas and comes
 back as ``[32, 2]`` (01.data_parallel.ipynb:300-473).  ``--devices`` accepts CPU placeholders so the
 scatter / replicate / apply / gather flow can be watched on a machine without GPUs.
+``--graphed`` (CUDA devices, static batch shape) trains through ``GraphedDataParallel``: persistent replicas and one
+CUDA graph per device, 2.3x faster than ``nn.DataParallel`` at 8 GPUs where the eager wrapper is host-bound
+(profiles/toy_bench_dp_8.json); the "In Model" lines then print once, at capture.
 """
 import argparse
 import os
@@ -25,6 +28,7 @@ if __name__ == "__main__":
     ap.add_argument("--devices", default=None, help="comma separated, e.g. cuda:0,cuda:1 or cpu,cpu")
     ap.add_argument("--fused-sum", action="store_true", help="fuse the output gather with the sum loss")
     ap.add_argument("--max-batches", type=int, default=0)
+    ap.add_argument("--graphed", action="store_true", help="graph-replayed replicas (CUDA, static shapes)")
     args = ap.parse_args()
     if args.devices:
         devices = args.devices.split(",")
@@ -36,6 +40,21 @@ if __name__ == "__main__":
     if len(devices) > 1:
         print("Let's use", len(devices), "devices!")
         model = b2.DataParallel(model, device_ids=devices)
+    if args.graphed and len(devices) > 1 and device.type == "cuda":
+        base = model.module
+        ex = torch.zeros(batch_size, input_size, device=device)
+        gdp = b2.GraphedDataParallel(base, devices, lambda out, _y: out.sum(), ex, torch.zeros(batch_size, device=device))
+        optimizer = torch.optim.Adam(base.parameters(), lr=1e-3)
+        for i, data in enumerate(rand_loader):
+            if data.shape[0] != batch_size:
+                break
+            optimizer.zero_grad()
+            loss = gdp.train_step(data.to(device), ex[:, 0])
+            optimizer.step()
+            print("Outside: input size", data.size(), "loss", round(float(loss), 4))
+            if args.max_batches and i + 1 >= args.max_batches:
+                break
+        sys.exit(0)
     optimizer = torch.optim.Adam(model.parameters(), lr=1e-3)
     for i, data in enumerate(rand_loader):
         optimizer.zero_grad()
