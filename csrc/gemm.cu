@@ -178,7 +178,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
   float* col_acc = reinterpret_cast<float*>(stage_out + 2 * kStageOutBytes);     // [4 quarters][2][256]
   Barriers* bars = reinterpret_cast<Barriers*>(stage_out + 2 * kStageOutBytes + p.colacc_bytes);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);     // provably warp-uniform
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
 
@@ -324,7 +324,9 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // The whole warp runs the loop (every value below is warp-uniform) and ONE elected lane issues each
+    // tcgen05.mma / commit: see umma_f16_elect.
+    {
       const bool a_mn = p.kind == 1;
       const bool b_mn = p.kind == 1 || p.b_mn;
       const uint32_t idesc = umma_idesc_bf16(kBM, p.BN, a_mn, b_mn);
@@ -361,10 +363,10 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
             // the tap's operand = the staged patch seen from pixel (dh + 1, dw + 1)
 #pragma unroll
             for (int k = 0; k < kBK / 16; ++k)
-              umma_f16(tmem_d, desc_a0 + (sa + halo_aoff[tap] + k * 2), desc_b0 + (sw0 + tap * 512 + k * (kstep_b >> 4)),
+              umma_f16_elect(tmem_d, desc_a0 + (sa + halo_aoff[tap] + k * 2), desc_b0 + (sw0 + tap * 512 + k * (kstep_b >> 4)),
                        idesc, (tap > 0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&bars->empty[stage]);
+          umma_commit_elect(&bars->empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         } else
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -375,12 +377,12 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
           const uint32_t sb = sa + (a_stage_bytes >> 4);
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k)
-            umma_f16(tmem_d, desc_a0 + (sa + k * (kstep_a >> 4)), desc_b0 + (sb + k * (kstep_b >> 4)), idesc,
+            umma_f16_elect(tmem_d, desc_a0 + (sa + k * (kstep_a >> 4)), desc_b0 + (sb + k * (kstep_b >> 4)), idesc,
                      (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit(&bars->empty[stage]);
+          umma_commit_elect(&bars->empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&bars->tmem_full[acc]);
+        umma_commit_elect(&bars->tmem_full[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }

@@ -144,6 +144,33 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same, executed by a whole (converged) warp: one elected lane issues.  With every operand warp-uniform the
+// compiler keeps descriptors and addresses in uniform registers; under `if (lane == 0)` it cannot prove that and
+// wraps every UTCHMMA in a waterfall loop (R2UR + ELECT + BRA.U.ANY, ~19 instructions per MMA -- more than the
+// 32-cycle floor of a 128 x 64 x 16 MMA can hide).
+__device__ __forceinline__ void umma_f16_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q;\n"
+      ".reg .b32 rx;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "elect.sync rx|q, 0xffffffff;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      ".reg .b32 rx;\n"
+      "elect.sync rx|q, 0xffffffff;\n"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+      "}\n" ::"r"(smem_u32(bar))
+      : "memory");
+}
 // Arrive on an mbarrier once every previously issued tcgen05.mma has completed.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
