@@ -210,10 +210,11 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    // One thread; the loops carry coordinates incrementally (no division per k-block) and use
-    // pre-computed 32-bit shared addresses, because this thread's instruction count per TMA
-    // issue bounds the rate at which short-K tiles can be fed.
-    if (lane == 0) {
+    // The whole warp runs the loops (every value is warp-uniform) and one elected lane issues each TMA /
+    // expect-tx; the loops carry coordinates incrementally (no division per k-block) and use pre-computed
+    // 32-bit shared addresses, because the instruction count per TMA issue bounds the rate at which
+    // short-K tiles can be fed.
+    {
       const uint32_t smem0 = smem_u32(smem);
       const uint32_t full0 = smem_u32(&bars->full[0]);
       int stage = 0;
@@ -223,18 +224,18 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       if (p.halo) {
         // resident filter: nine 64 x 64 blocks, loaded once per CTA
         const uint32_t sw0 = smem0 - kHaloW, wb = smem_u32(&bars->wfull);
-        mbar_expect_tx_s(wb, kHaloW);
+        mbar_expect_tx_e(wb, kHaloW);
         for (int tap = 0; tap < 9; ++tap) {
-          if (!p.b_mn) tma_load_2d_s(sw0 + tap * 8192, &maps.b[0], wb, tap * 64, 0);
-          else tma_load_2d_s(sw0 + tap * 8192, &maps.b[0], wb, p.taps[tap].pad * 64, 0);
+          if (!p.b_mn) tma_load_2d_e(sw0 + tap * 8192, &maps.b[0], wb, tap * 64, 0);
+          else tma_load_2d_e(sw0 + tap * 8192, &maps.b[0], wb, p.taps[tap].pad * 64, 0);
         }
         const uint32_t tx = (uint32_t)((p.bw + 2) * (p.bh + 2) * 128);
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
           mbar_wait(&bars->empty[stage], phase ^ 1);
           const uint32_t fb = full0 + stage * 8;
-          mbar_expect_tx_s(fb, tx);
+          mbar_expect_tx_e(fb, tx);
           // one box with a one-pixel halo all around; outside the image TMA fills zeros (= the padding)
-          tma_load_4d_s(smem0 + stage * stage_bytes, &maps.a[1], fb, 0, tc.d1 * p.bw - 1, tc.d2 * p.bh - 1, tc.d3);
+          tma_load_4d_e(smem0 + stage * stage_bytes, &maps.a[1], fb, 0, tc.d1 * p.bw - 1, tc.d2 * p.bh - 1, tc.d3);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       } else
@@ -259,17 +260,17 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
               mbar_wait(&bars->empty[stage], phase ^ 1);
               const uint32_t sa = smem0 + stage * stage_bytes;
               const uint32_t fb = full0 + stage * 8;
-              mbar_expect_tx_s(fb, stage_bytes);
-              tma_load_4d_s(sa, ma, fb, cb * kBK, wt, ht, n0);
+              mbar_expect_tx_e(fb, stage_bytes);
+              tma_load_4d_e(sa, ma, fb, cb * kBK, wt, ht, n0);
               if (!p.b_mn) {
-                tma_load_2d_s(sa + a_stage_bytes, &maps.b[0], fb, kcoord, nb0);
+                tma_load_2d_e(sa + a_stage_bytes, &maps.b[0], fb, kcoord, nb0);
               } else {
                 // MN-major B: rows = reduction index (this 64-block of it), columns = output
                 // channels of this tile, fetched as 64-wide chunks; tp.pad = filter tap index.
                 const int col0 = tp.pad * p.n_valid + nb0;
 #pragma unroll 1
                 for (int c = 0; c < (p.BN >> 6); ++c)
-                  tma_load_2d_s(sa + a_stage_bytes + c * 8192, &maps.b[0], fb, col0 + c * 64, cb * kBK);
+                  tma_load_2d_e(sa + a_stage_bytes + c * 8192, &maps.b[0], fb, col0 + c * 64, cb * kBK);
               }
               if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -307,13 +308,13 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
             const uint32_t sa = smem0 + stage * stage_bytes;
             const uint32_t sb = sa + a_stage_bytes;
             const uint32_t fb = full0 + stage * 8;
-            mbar_expect_tx_s(fb, tx_bytes);
+            mbar_expect_tx_e(fb, tx_bytes);
             // A = dY^T : two 64-wide chunks of output channels, 64 pixels deep.
-            tma_load_4d_s(sa, &maps.a[0], fb, m0, w0, h0, n0);
-            tma_load_4d_s(sa + 8192, &maps.a[0], fb, m0 + 64, w0, h0, n0);
+            tma_load_4d_e(sa, &maps.a[0], fb, m0, w0, h0, n0);
+            tma_load_4d_e(sa + 8192, &maps.a[0], fb, m0 + 64, w0, h0, n0);
 #pragma unroll
             for (int c = 0; c < 4; ++c)
-              if (c < nvalid) tma_load_4d_s(sb + c * 8192, mb[c], fb, cc0[c], w0 + cdw[c], h0 + cdh[c], n0);
+              if (c < nvalid) tma_load_4d_e(sb + c * 8192, mb[c], fb, cc0[c], w0 + cdw[c], h0 + cdh[c], n0);
             w0 += p.bw;
             if (w0 >= wend) { w0 = 0; h0 += p.bh; if (h0 >= hend) { h0 = 0; n0 += p.bn; } }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }

@@ -112,6 +112,33 @@ __device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
                : "memory");
 }
 
+// Elected-lane forms for a converged warp running the producer loop as a whole (see umma_f16_elect: with
+// warp-uniform operands there is no waterfall loop around the uniform-datapath instruction).
+#define B200_ELECT_PROLOGUE ".reg .pred q;\n.reg .b32 rx;\nelect.sync rx|q, 0xffffffff;\n"
+__device__ __forceinline__ void tma_load_2d_e(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                              int c0, int c1) {
+  asm volatile(
+      "{\n" B200_ELECT_PROLOGUE
+      "@q cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];\n}\n"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_e(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                              int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "{\n" B200_ELECT_PROLOGUE
+      "@q cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];\n}\n"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_e(uint32_t bar, uint32_t bytes) {
+  asm volatile("{\n" B200_ELECT_PROLOGUE "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n}\n"
+               ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result) {
