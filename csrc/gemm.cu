@@ -399,6 +399,9 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
     uint8_t* buf = stage_out + (warp - 2) * 4096;
     int acc = 0;
     uint32_t acc_phase = 0;
+    // which copy of the statistics this CTA adds into (one modulo per kernel, not per tile)
+    const size_t stat_copy_off =
+        p.bn_sums != nullptr ? (size_t)(p.det ? blockIdx.x : blockIdx.x % p.bn_used) * 2 * p.bn_C : 0;
     TileCoord tc;
     tile_init(p, blockIdx.x, tc);
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tile_next(p, tc)) {
@@ -413,7 +416,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * p.BN;
       if (p.tma_store) {
         const int cols_per_slab = p.out_fp32 ? 32 : 64;
-        const int nslabs = p.BN / cols_per_slab;
+        const int nslabs = p.out_fp32 ? (p.BN >> 5) : (p.BN >> 6);        // (no division in the tile loop)
         int c1, c2, c3;                    // origin of this warp's 32-row sub-box in the output map
         if (p.kind == 0) {
           c1 = tw * p.bw + p.qoff[q][0]; c2 = th * p.bh + p.qoff[q][1]; c3 = tn * p.bn + p.qoff[q][2];
@@ -424,7 +427,8 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         const int sw = lane & 7;
         // halo tiles may hang over the image edge: those rows are clipped by the TMA store, but they must not
         // enter the fused statistics (their 3x3 windows still touch valid pixels), so they are staged as zeros
-        const bool zero_row = p.halo && (th * p.bh + row / p.bw >= p.H || tw * p.bw + row % p.bw >= p.W);
+        // (halo tiles are always 8 pixels wide: shifts, not divisions, once per tile per thread)
+        const bool zero_row = p.halo && (th * p.bh + (row >> 3) >= p.H || tw * 8 + (row & 7) >= p.W);
         const bool plain = (p.bias == nullptr) && !p.relu;       // uniform across the CTA
         for (int sl = pi; sl < nslabs; sl += 2) {
           const int col0 = col_base + sl * cols_per_slab;
@@ -614,7 +618,7 @@ tc_gemm_kernel(const __grid_constant__ TmaMaps maps, const __grid_constant__ Gem
         float* accb = col_acc;
         // det: this CTA owns copy blockIdx.x and column c is always handled by the same thread, so a
         // plain read-modify-write in tile order replaces the atomics
-        float* dstb = p.bn_sums + (size_t)(p.det ? blockIdx.x : blockIdx.x % p.bn_used) * 2 * p.bn_C;
+        float* dstb = p.bn_sums + stat_copy_off;
         const int e = (warp - 2) * 32 + lane;          // 0..255: one column per thread
         if (e < p.BN) {
           const int c = col_base + e;
