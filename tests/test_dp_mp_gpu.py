@@ -234,10 +234,14 @@ def test_data_parallel_replica_cache_and_kernel_scatter_gather():
     assert pc["hits"] >= 3 and pc["misses"] >= 1
     misses = pc["misses"]
     x = torch.randn(8 * n, 64, device="cuda:0"); y = torch.randn(8 * n, 16, device="cuda:0")
+    seen = []
     for it in range(3):
         opt.zero_grad(); torch.nn.functional.mse_loss(dp(x).float(), y).backward(); opt.step()
         ropt.zero_grad(); torch.nn.functional.mse_loss(rdp(x), y).backward(); ropt.step()
-    assert pc["misses"] == misses + 3                # every optimizer step invalidated the replicas
+        seen.append(pc["misses"])
+    # every optimizer step invalidated the replicas: each forward after one is a miss.  (The first forward of the
+    # loop is a miss only if the last ragged batch above used fewer devices: the device set is part of the key.)
+    assert seen[1] == seen[0] + 1 and seen[2] == seen[1] + 1 and seen[0] in (misses, misses + 1)
     for p, q in zip(m.parameters(), ref.parameters()):
         assert torch.allclose(p, q, atol=2e-2, rtol=2e-2)
     # gather of scalars (one per replica) and the gradient scatter behind it
