@@ -152,11 +152,16 @@ def lib() -> "_Counted":
         return _lib
 
 
+_mode_listeners: list = []      # callbacks run when a library-wide mode changes (caches keyed on it)
+
+
 def set_deterministic(on: bool = True) -> None:
     """Fixed-order reductions in every kernel of the library (BatchNorm statistics, split-K weight gradients,
     bias gradients): the same step on the same inputs gives the same bits.  Also settable with
     ``B200DT_DETERMINISTIC=1`` in the environment.  Slower; meant for regression tests and debugging."""
     lib().b200dt_set_deterministic(int(bool(on)))
+    for fn in _mode_listeners:
+        fn()
 
 
 def is_deterministic() -> bool:

@@ -10,6 +10,7 @@ from typing import Optional, Tuple
 
 import torch
 
+from .. import _lib as _lib_mod
 from .._lib import check, lib, on_device, ptr, stream_ptr
 
 BF16 = torch.bfloat16
@@ -22,8 +23,15 @@ def bn_replicas() -> int:
     return int(lib().b200dt_bn_replicas())
 
 
+_used_cache: dict = {}          # C -> copies; cleared when the deterministic switch changes (_lib.set_deterministic)
+_lib_mod._mode_listeners.append(_used_cache.clear)
+
+
 def bn_replicas_used(C: int) -> int:
-    return int(lib().b200dt_bn_replicas_used(int(C)))
+    r = _used_cache.get(C)
+    if r is None:
+        r = _used_cache[C] = int(lib().b200dt_bn_replicas_used(int(C)))
+    return r
 
 
 # Zero-filled scratch for the statistics kernels.  Every conv-with-statistics, bn_stats and bn_bwd_reduce launch
@@ -36,27 +44,36 @@ _ZERO_CHUNK_FLOATS = 1 << 20
 _zero_chunks: dict = {}
 
 
+_zero_fns = None          # (capture_id, get_prezeroed, set_prezeroed) bound once: this runs ~100x per step
+
+
 def zeroed_floats(n: int, device) -> torch.Tensor:
     """``n`` fp32 zeros on ``device`` (256-byte aligned), valid for ONE accumulate-into use on the current stream."""
-    device = torch.device(device)
+    if not isinstance(device, torch.device):
+        device = torch.device(device)
     if device.type != "cuda":
         return torch.zeros(n, device=device, dtype=F32)
-    L = lib()
-    if not L.b200dt_get_sums_prezeroed():
-        L.b200dt_set_sums_prezeroed(1)
-    n64 = (int(n) + 63) // 64 * 64
-    idx = device.index if device.index is not None else torch.cuda.current_device()
-    st = torch.cuda.current_stream(idx).cuda_stream
-    cap = int(L.b200dt_capture_id(st))
-    key = (idx, st)
-    ent = _zero_chunks.get(key)
-    if ent is None or ent[2] != cap or ent[1] + n64 > ent[0].numel():
+    global _zero_fns
+    if _zero_fns is None:
+        h = lib()._handle
+        _zero_fns = (h.b200dt_capture_id, h.b200dt_get_sums_prezeroed, h.b200dt_set_sums_prezeroed)
+        if not _zero_fns[1]():
+            _zero_fns[2](1)
+    idx = device.index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    st = stream_ptr(idx)
+    cap = _zero_fns[0](st)
+    n64 = (n + 63) & ~63
+    ent = _zero_chunks.get((idx, st))
+    if ent is None or ent[2] != cap or ent[1] + n64 > ent[3]:
+        size = max(_ZERO_CHUNK_FLOATS, n64)
         with torch.cuda.device(idx):
-            ent = [torch.zeros(max(_ZERO_CHUNK_FLOATS, n64), device=device, dtype=F32), 0, cap]
-        _zero_chunks[key] = ent
-    out = ent[0][ent[1]:ent[1] + n]
-    ent[1] += n64
-    return out
+            ent = [torch.zeros(size, device=device, dtype=F32), 0, cap, size]
+        _zero_chunks[(idx, st)] = ent
+    off = ent[1]
+    ent[1] = off + n64
+    return ent[0].narrow(0, off, n)
 
 
 def _need(t: torch.Tensor, dtype, name: str) -> None:
