@@ -1,7 +1,7 @@
 """world=1 run of the fused collective (gather -> reduce -> scatter on local staging only): isolates the
 HBM-side cost of the kernel phases from NVLink."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from pytorch_distributed_training_tutorials_b200 import group
 from pytorch_distributed_training_tutorials_b200.ops import collectives as coll

@@ -1,5 +1,5 @@
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
 from pytorch_distributed_training_tutorials_b200.ops import functional as Fn

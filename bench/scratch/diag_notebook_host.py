@@ -1,8 +1,9 @@
 """cProfile of the notebook's train() workload on this library (eager, single GPU): where the host time goes."""
 import cProfile, io, os, pstats, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
-from bench.mp_bench import train_ours, num_classes
+sys.path.insert(0, os.path.join(sys.path[0], 'bench'))
+from mp_bench import train_ours, num_classes
 from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
 from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD
 

@@ -1,7 +1,7 @@
 """Does the two-stage pipeline overlap? Per-device busy time and cross-device overlap of one step,
 from torch.profiler kernel timestamps (diagnostic only: numbers under a profiler are not bench values)."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from torch.profiler import profile, ProfilerActivity
 from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50, PipelineParallelResNet50

@@ -1,7 +1,7 @@
 """Gradient agreement of the own-kernel ResNet-50 with torchvision fp32, with torchvision-under-autocast
 as the yardstick for what bf16 costs on the same batch."""
 import sys, os, copy
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch, torchvision
 import torch.nn.functional as F
 from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50

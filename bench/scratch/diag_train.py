@@ -1,5 +1,5 @@
 import sys, os, copy
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch, torchvision
 import torch.nn.functional as F
 from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50

@@ -1,6 +1,6 @@
 """Host-side profile + device timeline split of one DataParallel MLP step (diagnostics)."""
 import sys, os, cProfile, pstats, io, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import pytorch_distributed_training_tutorials_b200 as b2
 from pytorch_distributed_training_tutorials_b200.models.toy import MLP

@@ -25,7 +25,7 @@ def test_resnet50_matches_torchvision():
     F.cross_entropy(out_ref, y).backward()
     # yardstick: what bf16 compute costs the library stack itself on this batch: torchvision under
     # autocast vs the fp32 run above (at random init the gradients below the last block are
-    # dominated by bf16 rounding for BOTH stacks; bench/diag_resnet_grads.py prints the table)
+    # dominated by bf16 rounding for BOTH stacks; bench/scratch/diag_resnet_grads.py prints the table)
     import copy
     amp = copy.deepcopy(ref)
     amp.zero_grad()
