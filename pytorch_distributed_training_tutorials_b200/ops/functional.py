@@ -50,7 +50,17 @@ def _grad_out(p: torch.Tensor) -> Optional[torch.Tensor]:
     return region[off:off + p.numel()].view(p.shape)
 
 
-class _Linear(torch.autograd.Function):
+class _Fn(torch.autograd.Function):
+    """``Function.apply`` minus the functorch-wrapper bookkeeping torch runs on every call (3 us per op, ~100 ops per
+    ResNet-50 step: eager steps here are bound by the host).  vmap / functorch transforms over these ops are not
+    supported either way: they are opaque kernel launches."""
+
+    @classmethod
+    def apply(cls, *args):
+        return super(torch.autograd.Function, cls).apply(*args)
+
+
+class _Linear(_Fn):
     @staticmethod
     def forward(ctx, x, weight, bias, relu, out_fp32):
         wb = _shadow(weight)
@@ -104,7 +114,7 @@ class _Linear(torch.autograd.Function):
         return dx, dw, db, None, None
 
 
-class _SkinnyLinear(torch.autograd.Function):
+class _SkinnyLinear(_Fn):
     """fp32 Linear for feature counts the tensor-core path cannot take (the tutorial's Linear(20,1),
     (32,2), (10000,10), (10,5); ddp_gpus.py:81, 01.data_parallel.ipynb:171, 03.model_parallel.ipynb:444-446)."""
 
@@ -139,7 +149,7 @@ def linear(x, weight, bias=None, relu: bool = False, out_fp32: bool = False):
     return _Linear.apply(x, weight, bias, relu, out_fp32)
 
 
-class _Conv2d(torch.autograd.Function):
+class _Conv2d(_Fn):
     @staticmethod
     def forward(ctx, x, weight, stride, with_stats):
         wb = _shadow(weight)
@@ -177,7 +187,7 @@ def conv2d(x, weight, stride: int = 1, with_stats: bool = False):
     return _Conv2d.apply(x, weight, stride, with_stats)
 
 
-class _ConvSkip(torch.autograd.Function):
+class _ConvSkip(_Fn):
     """``(conv(x, w), x)``: the convolution that opens a residual block together with the block's
     identity branch, so that backward can add the two gradients of ``x`` inside the dgrad epilogue
     (TMA reduce-add into the incoming skip gradient) instead of leaving a separate add to autograd."""
@@ -219,7 +229,7 @@ def conv2d_skip(x, weight, stride: int = 1, with_stats: bool = False):
     return _ConvSkip.apply(x, weight, stride, with_stats)
 
 
-class _ConvDual(torch.autograd.Function):
+class _ConvDual(_Fn):
     """Two convolutions of the same input (a block's first conv and its downsample projection):
     backward writes the first data gradient and adds the second one in its epilogue."""
 
@@ -274,7 +284,7 @@ def _stem_operand(w: torch.Tensor) -> torch.Tensor:
     return wk
 
 
-class _StemConv(torch.autograd.Function):
+class _StemConv(_Fn):
     """7x7 stride-2 pad-3 convolution of the fp32 NCHW network input (Cin = 3)."""
 
     @staticmethod
@@ -327,7 +337,7 @@ def stem_conv(x_nchw_f32, weight, with_stats: bool = False):
     return _StemConv.apply(x_nchw_f32, weight, with_stats)
 
 
-class _BatchNorm(torch.autograd.Function):
+class _BatchNorm(_Fn):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, training, sums,
                 tracked=None):
@@ -382,7 +392,7 @@ def batch_norm(x, gamma, beta, running_mean, running_var, residual=None, eps: fl
                             sums, num_batches_tracked)
 
 
-class _MaxPool(torch.autograd.Function):
+class _MaxPool(_Fn):
     @staticmethod
     def forward(ctx, x):
         y, arg = NV.maxpool_fwd(x.contiguous())
@@ -400,7 +410,7 @@ def max_pool_3x3_s2(x):
     return _MaxPool.apply(x)
 
 
-class _AvgPool(torch.autograd.Function):
+class _AvgPool(_Fn):
     @staticmethod
     def forward(ctx, x):
         ctx.shape = x.shape
@@ -416,7 +426,7 @@ def global_avg_pool(x):
     return _AvgPool.apply(x)
 
 
-class _Loss(torch.autograd.Function):
+class _Loss(_Fn):
     @staticmethod
     def forward(ctx, kind, pred, target):
         pred_c = pred.contiguous()

@@ -27,6 +27,7 @@ class _DeviceTable:
     def __init__(self, device: torch.device) -> None:
         self.device = device
         self.key = None
+        self.fast_key = None          # (param ptrs..., grad ptrs...) of the last update: see _FusedBase._table
         self.meta = None
         self.chunks = None
         self.n_chunks = 0
@@ -97,6 +98,26 @@ class _FusedBase(Optimizer):
                 cpu.append(p)
         return by_dev, cpu
 
+    def _table(self, gi: int, dev: torch.device, ps, build_rows) -> "_DeviceTable":
+        """The device table of (param group, device), rebuilt only when a parameter or gradient address changed.
+        In steady state the caching allocator hands every gradient the address it had a step ago, so a step costs
+        2 x len(ps) ``data_ptr()`` calls and one tuple compare instead of building and hashing the row lists
+        (1.2 ms of an 11 ms host-bound ResNet-50 step).  Optimizer state tensors (bf16 shadows, Adam moments) are
+        created once and keep their addresses; ``load_state_dict`` drops the fast keys."""
+        tab = self._tables.get((gi, dev))
+        if tab is None:
+            tab = self._tables[(gi, dev)] = _DeviceTable(dev)
+        fast = tuple([p.data_ptr() for p in ps] + [p.grad.data_ptr() for p in ps])
+        if tab.fast_key != fast:
+            tab.update(build_rows())
+            tab.fast_key = fast
+        return tab
+
+    def load_state_dict(self, state_dict) -> None:
+        super().load_state_dict(state_dict)
+        for tab in self._tables.values():
+            tab.fast_key = None
+
     def refresh_shadows(self) -> None:
         """Re-derive the bf16 operand copies from the fp32 masters (after the masters were written by
         something other than ``step``: a checkpoint load, a restore after warm-up iterations)."""
@@ -137,13 +158,14 @@ class FusedSGD(_FusedBase):
         for gi, group in enumerate(self.param_groups):
             by_dev, slow = self._cuda_groups(group)
             for dev, ps in by_dev.items():
-                rows = []
-                for p in ps:
-                    sh = self._shadow_for(p)
-                    rows.append([p.data_ptr(), p.grad.data_ptr(), sh.data_ptr() if sh is not None else 0,
-                                 p.numel(), 0, 0, 0, 0])
-                tab = self._tables.setdefault((gi, dev), _DeviceTable(dev))
-                tab.update(rows)
+                def rows(ps=ps):
+                    out = []
+                    for p in ps:
+                        sh = self._shadow_for(p)
+                        out.append([p.data_ptr(), p.grad.data_ptr(), sh.data_ptr() if sh is not None else 0,
+                                    p.numel(), 0, 0, 0, 0])
+                    return out
+                tab = self._table(gi, dev, ps, rows)
                 with torch.cuda.device(dev):
                     check(lib().b200dt_multi_sgd(ptr(tab.meta), ptr(tab.chunks), tab.n_chunks, group["lr"],
                                                  group["weight_decay"], grad_scale, int(self.fuse_zero_grad),
