@@ -19,6 +19,18 @@ for line in open(os.path.join(ROOT, "gpurun_out/ncu/plain.jsonl")):
     except Exception:
         pass
 
+# families captured in an earlier call of the round (every gpurun box is fresh and ncu_all.sh starts a new plain.jsonl):
+# their un-profiled time is carried over from the table this script wrote last time
+prev_md = os.path.join(ROOT, "profiles/ncu_summaries.md")
+if os.path.exists(prev_md):
+    for line in open(prev_md):
+        cells = [c.strip() for c in line.strip().strip("|").split("|")]
+        if len(cells) == 12 and cells[0] not in plain and cells[0] not in ("family", "---"):
+            try:
+                plain[cells[0]] = {"family": cells[0], "ms": float(cells[4]), "flops": 0}
+            except ValueError:
+                pass
+
 WANT = {"gpu__time_duration.sum": "dur", "dram__bytes_read.sum": "rd", "dram__bytes_write.sum": "wr",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram_pct",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active": "tensor_pct",
