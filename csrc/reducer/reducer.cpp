@@ -15,6 +15,7 @@
 //
 // Counterpart in the reference's stack: c10d::Reducer, reached from
 // /root/reference/ddp_gpus.py:32,38 (spec: torch/csrc/distributed/c10d/reducer.hpp).
+#include "linear.h"
 #include <torch/extension.h>
 #include <torch/csrc/autograd/engine.h>
 #include <torch/csrc/autograd/utils/lambda_post_hook.h>
@@ -503,7 +504,11 @@ class Reducer {
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
-  m.doc() = "b200 gradient reducer (autograd hooks, bucket bookkeeping, launch ordering)";
+  m.doc() = "b200 gradient reducer (autograd hooks, bucket bookkeeping, launch ordering) + C++ autograd Linear";
+  m.def("linear_set_fns", &b200_linear_set_fns, "addresses of b200dt_gemm_tn/nn/nt_reduce_bf16 and b200dt_relu_bwd_bias");
+  m.def("linear", &b200_linear, py::arg("x"), py::arg("weight"), py::arg("wb"), py::arg("bias"), py::arg("relu"),
+        py::arg("out_fp32"), "y = x W^T + b (ReLU) with a C++ backward node (no GIL in backward)");
+  m.def("linear_launches", &b200_linear_launches);
   m.def("assign_buckets", &assign_buckets, py::arg("tensors"), py::arg("caps"),
         py::arg("tensor_indices") = std::vector<int64_t>{},
         "Greedy size-capped bucket assignment; index-exact with torch's "

@@ -144,8 +144,41 @@ def skinny_linear(x, weight, bias=None):
     return _SkinnyLinear.apply(x, weight, bias)
 
 
+_cpp_linear = None          # the C++ extension once its kernel addresses are registered; False = not available / off
+
+
+def _native_linear():
+    """csrc/reducer/linear.cpp: the same forward / backward as ``_Linear`` as a C++ autograd node, so the backward
+    passes of DataParallel replicas (one autograd thread per device) do not serialise on the GIL.
+    ``B200DT_CPP_LINEAR=0`` keeps the Python node."""
+    global _cpp_linear
+    if _cpp_linear is None:
+        _cpp_linear = False
+        if os.environ.get("B200DT_CPP_LINEAR", "1") not in ("0", ""):
+            try:
+                import ctypes as C
+                from .._lib import lib
+                from ..parallel._native_reducer import load
+                mod = load()
+                h = lib()._handle
+                addr = lambda name: C.cast(getattr(h, name), C.c_void_p).value
+                mod.linear_set_fns(addr("b200dt_gemm_tn_bf16"), addr("b200dt_gemm_nn_bf16"),
+                                   addr("b200dt_gemm_nt_reduce_bf16"), addr("b200dt_relu_bwd_bias"))
+                _cpp_linear = mod
+            except Exception:      # noqa: BLE001 -- no extension / old build: the Python node does the same work
+                _cpp_linear = False
+    return _cpp_linear
+
+
 def linear(x, weight, bias=None, relu: bool = False, out_fp32: bool = False):
     """y = x @ weight^T + bias on tcgen05; needs in_features % 8 == 0 (TMA row pitch)."""
+    if (x.is_cuda and weight.shape[0] % 8 == 0 and weight.shape[1] % 8 == 0 and weight.dtype == F32
+            and getattr(weight, "_b200_grad_slot", None) is None and (bias is None or bias.dtype == F32)):
+        mod = _native_linear()
+        if mod:
+            from .. import _lib
+            _lib.launch_count += 1 + (3 if torch.is_grad_enabled() and (weight.requires_grad or x.requires_grad) else 0)
+            return mod.linear(x, weight, _shadow(weight), bias, bool(relu), bool(out_fp32))
     return _Linear.apply(x, weight, bias, relu, out_fp32)
 
 
