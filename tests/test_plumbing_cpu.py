@@ -477,3 +477,18 @@ def test_launcher_accepts_torchrun_rendezvous_spelling():
     assert a.training_script == "train.py" and a.training_script_args == ["--max_epochs", "3"]
     b = parse_args(["--rdzv_endpoint", "localhost", "train.py"])
     assert (b.master_addr, b.master_port) == ("localhost", 29500)
+
+
+def test_native_linear_extension_is_built_and_switchable(monkeypatch):
+    """The C++ autograd Linear lives in the reducer extension; its kernel addresses come from the ctypes handle, and
+    ``B200DT_CPP_LINEAR=0`` keeps the Python node (the two are interchangeable; parity is tested on the GPU)."""
+    from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
+    from pytorch_distributed_training_tutorials_b200.parallel._native_reducer import load
+    mod = load()
+    assert hasattr(mod, "linear") and hasattr(mod, "linear_set_fns") and mod.linear_launches() >= 0
+    monkeypatch.setattr(Fn, "_cpp_linear", None)
+    monkeypatch.setenv("B200DT_CPP_LINEAR", "0")
+    assert Fn._native_linear() is False
+    monkeypatch.setattr(Fn, "_cpp_linear", None)
+    monkeypatch.setenv("B200DT_CPP_LINEAR", "1")
+    assert Fn._native_linear() is mod
