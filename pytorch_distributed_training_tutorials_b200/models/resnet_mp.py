@@ -48,7 +48,8 @@ class ModelParallelResNet50(ResNet):
         mb = example_x[: max(1, example_x.shape[0] // chunks)].to(dev0)
         times = profile_units(units, mb, reps=reps, module=probe)
         del probe, units
-        torch.cuda.empty_cache()
+        if dev0.type == "cuda":
+            torch.cuda.empty_cache()
         cut = balanced_cuts(times, 2)[0]
         cut = min(cut, len(names) - 2)
         model = cls(split_after=names[cut], **kw)

@@ -70,6 +70,11 @@ class Conv2d(nn.Module):
 
     def forward(self, x: torch.Tensor, with_stats: bool = False):
         """``with_stats=True`` -> ``(y, sums)`` for a following ``BatchNorm2d(y, sums=sums)``."""
+        if not x.is_cuda:
+            # CPU reference path (plain torch, same NHWC interface): debugging and the CPU test-suite
+            y = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), self.weight.permute(0, 3, 1, 2).to(x.dtype),
+                                           stride=self.stride, padding=self.kernel_size // 2).permute(0, 2, 3, 1)
+            return (y, None) if with_stats else y
         return Fn.conv2d(x, self.weight, self.stride, with_stats)
 
     def extra_repr(self) -> str:
@@ -89,6 +94,10 @@ class StemConv(nn.Module):
         self._register_load_state_dict_pre_hook(_import_oihw, with_module=True)
 
     def forward(self, x: torch.Tensor, with_stats: bool = False):
+        if not x.is_cuda:
+            y = torch.nn.functional.conv2d(x, self.weight.permute(0, 3, 1, 2).to(x.dtype), stride=2,
+                                           padding=3).permute(0, 2, 3, 1)
+            return (y, None) if with_stats else y
         return Fn.stem_conv(x, self.weight, with_stats)
 
 
@@ -120,6 +129,16 @@ class BatchNorm2d(nn.Module):
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None,
                 sums: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if not x.is_cuda:
+            # CPU reference path: torch's batch_norm on the NCHW view, then the fused tail in plain ops
+            if self.training:
+                self.num_batches_tracked += 1
+            y = torch.nn.functional.batch_norm(x.permute(0, 3, 1, 2), self.running_mean, self.running_var,
+                                               self.weight, self.bias, self.training, self.momentum,
+                                               self.eps).permute(0, 2, 3, 1)
+            if residual is not None:
+                y = y + residual
+            return torch.relu(y) if self.relu else y
         # the step counter is bumped by the apply kernel itself (53 fewer launches per ResNet-50 step)
         return Fn.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, residual,
                              self.eps, self.momentum, self.relu, self.training, sums,
@@ -131,11 +150,15 @@ class BatchNorm2d(nn.Module):
 
 class MaxPool3x3s2(nn.Module):
     def forward(self, x):
+        if not x.is_cuda:
+            return torch.nn.functional.max_pool2d(x.permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)
         return Fn.max_pool_3x3_s2(x)
 
 
 class GlobalAvgPool(nn.Module):
     def forward(self, x):
+        if not x.is_cuda:
+            return x.mean((1, 2))
         return Fn.global_avg_pool(x)
 
 

@@ -103,6 +103,27 @@ def profile_units(units: Sequence[Callable], x: torch.Tensor, reps: int = 3,
     saved = [b.detach().clone() for b in module.buffers()] if module is not None else []
     times: List[float] = []
     cur = x
+    if x.device.type != "cuda":
+        # CPU placeholders (tests, debugging): wall-clock time of the eager forward + backward
+        import time
+        for f in units:
+            xin = cur.detach().requires_grad_(cur.is_floating_point())
+            best, y = float("inf"), None
+            for _ in range(max(1, reps)):
+                xin.grad = None
+                t0 = time.perf_counter()
+                y = f(xin)
+                y.backward(torch.ones_like(y))
+                best = min(best, (time.perf_counter() - t0) * 1e3)
+            times.append(best)
+            cur = y.detach()
+        if module is not None:
+            with torch.no_grad():
+                for b, s in zip(module.buffers(), saved):
+                    b.copy_(s)
+            for p in module.parameters():
+                p.grad = None
+        return times
     with torch.cuda.device(x.device):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         side = torch.cuda.Stream()
