@@ -4,7 +4,8 @@
     python examples/model_parallel_demo.py resnet     # ResNet-50 split after layer2, naive vs pipelined
     python examples/model_parallel_demo.py place      # LLaMA-shaped stack auto-placed over the GPUs
 
-``toy`` and ``place`` accept ``--cpu`` to walk through the same code with CPU placeholders.
+Every mode accepts ``--cpu`` to walk through the same code with CPU placeholders (``resnet --cpu`` runs the naive and
+the eager pipelined split on the modules' plain-torch reference path; the CUDA-graph replay needs GPUs).
 """
 import argparse
 import os
@@ -32,16 +33,19 @@ def toy(cpu: bool) -> None:
     print("one optimizer step over parameters on two devices: ok, loss device", outputs.device)
 
 
-def resnet() -> None:
+def resnet(cpu: bool = False) -> None:
     from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
     from pytorch_distributed_training_tutorials_b200.models.resnet_mp import ModelParallelResNet50, PipelineParallelResNet50
     from pytorch_distributed_training_tutorials_b200.parallel.model_parallel import model_size
+    dev = dict(dev0="cpu", dev1="cpu") if cpu else {}
     print("resnet50 parameters:", model_size(resnet50(num_classes=1000)))
-    mp = ModelParallelResNet50(num_classes=1000)
+    mp = ModelParallelResNet50(num_classes=1000, **dev)
     print("split resnet50 parameters:", model_size(mp), "| stage devices:", mp.conv1.weight.device, mp.fc.weight.device)
-    pp = PipelineParallelResNet50(split_size=20, num_classes=1000)
-    x = torch.randn(120, 3, 128, 128)
-    print("naive:", tuple(mp(x).shape), "pipelined:", tuple(pp(x).shape))
+    pp = PipelineParallelResNet50(split_size=4 if cpu else 20, num_classes=1000, split_after="layer2.1", **dev)
+    x = torch.randn(8, 3, 64, 64) if cpu else torch.randn(120, 3, 128, 128)
+    print("naive:", tuple(mp(x).shape), "pipelined (cut after layer2.1):", tuple(pp(x).shape))
+    if cpu:
+        return
     # the fast pipelined form: every (stage, micro-batch) is captured once and replayed from CUDA graphs
     from pytorch_distributed_training_tutorials_b200.ops import functional as Fn
     from pytorch_distributed_training_tutorials_b200.ops.optim import FusedSGD
@@ -77,4 +81,4 @@ if __name__ == "__main__":
     ap.add_argument("what", choices=["toy", "resnet", "place"])
     ap.add_argument("--cpu", action="store_true")
     a = ap.parse_args()
-    {"toy": lambda: toy(a.cpu), "resnet": resnet, "place": lambda: place(a.cpu)}[a.what]()
+    {"toy": lambda: toy(a.cpu), "resnet": lambda: resnet(a.cpu), "place": lambda: place(a.cpu)}[a.what]()

@@ -492,3 +492,15 @@ def test_native_linear_extension_is_built_and_switchable(monkeypatch):
     monkeypatch.setattr(Fn, "_cpp_linear", None)
     monkeypatch.setenv("B200DT_CPP_LINEAR", "1")
     assert Fn._native_linear() is mod
+
+
+def test_model_parallel_demo_resnet_walks_through_on_cpu():
+    """examples/model_parallel_demo.py resnet --cpu: the reference's split (03.model_parallel.ipynb:807-833), naive and
+    pipelined, on CPU placeholders; both print torchvision's parameter count (ibid. 857, 888)."""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "examples", "model_parallel_demo.py"), "resnet", "--cpu"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.count("25557032") == 2
+    assert "naive: (8, 1000) pipelined (cut after layer2.1): (8, 1000)" in out.stdout
