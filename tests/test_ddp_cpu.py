@@ -164,3 +164,43 @@ def test_debug_handshake_catches_desynchronised_collectives():
     with pytest.raises(ProcessRaisedException) as ei:
         spawn(_handshake_mismatch, args=(2, _find_port()), nprocs=2)
     assert "collective mismatch" in str(ei.value)
+
+
+def _resnet_ddp(rank, world, port, out_dir):
+    """ResNet-50 (the modules' CPU reference path) under DDP over gloo: rank 0's parameters and BatchNorm buffers are
+    broadcast, gradients are averaged over the ranks, replicas stay identical step after step."""
+    from pytorch_distributed_training_tutorials_b200.models.resnet import resnet50
+    _setup(rank, world, port)
+    torch.manual_seed(100 + rank)                       # different init per rank
+    model = resnet50(num_classes=8)
+    ddp = DDP(model)
+    opt = torch.optim.SGD(ddp.parameters(), lr=0.01)
+    g = torch.Generator().manual_seed(50 + rank)        # different data per rank
+
+    def same_everywhere(t):
+        got = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(got, t.detach().contiguous())
+        return all(torch.equal(x, got[0]) for x in got)
+
+    assert all(same_everywhere(p) for p in list(model.parameters())[::20])
+    for it in range(2):
+        x = torch.randn(2, 3, 32, 32, generator=g); y = torch.randint(0, 8, (2,), generator=g)
+        opt.zero_grad()
+        torch.nn.functional.cross_entropy(ddp(x), y).backward()
+        assert all(same_everywhere(p.grad) for p in list(model.parameters())[::20]), it
+        opt.step()
+    assert all(same_everywhere(p) for p in model.parameters())
+    # buffers: every forward starts from rank 0's running statistics (broadcast_buffers=True, the reference's default)
+    ddp(torch.randn(2, 3, 32, 32, generator=g))
+    model.eval()
+    with torch.no_grad():
+        ddp(torch.randn(2, 3, 32, 32, generator=g))      # eval forward: broadcast, no update
+    assert same_everywhere(model.bn1.running_mean) and same_everywhere(model.layer4[2].bn3.running_var)
+    assert int(model.bn1.num_batches_tracked) == 3
+    group.destroy()
+    open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+
+
+def test_resnet50_ddp_over_gloo_keeps_replicas_identical(tmp_path):
+    spawn(_resnet_ddp, args=(2, _find_port(), str(tmp_path)), nprocs=2)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
