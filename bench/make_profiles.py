@@ -123,12 +123,14 @@ def misc():
             if k.endswith("_ms") and isinstance(v, (int, float)):
                 out.append(f"| {k[:-3]} | {v:.2f} | {d['batch'] / v * 1e3:.0f} |")
         open(os.path.join(P, "pipeline_bench.md"), "w").write("\n".join(out) + "\n")
-    for name, title in (("launches_bs32.csv", "batch 32"),):
-        f = os.path.join(G, name)
+    for b in (8, 64):
+        f = os.path.join(G, f"launches_{b}.csv")
         if os.path.exists(f):
             txt = subprocess.run([sys.executable, os.path.join(ROOT, "bench", "agg_launches.py"), f], capture_output=True, text=True).stdout
-            open(os.path.join(P, "launches_resnet50_step_bs32.md"), "w").write(
-                "# Same launch list at batch 32 (where the per-launch fixed costs show)\n\n```\n" + txt + "```\n")
+            open(os.path.join(P, f"launches_resnet50_step_bs{b}.md"), "w").write(
+                f"# Launch list of one ResNet-50 step at batch {b} (where the per-launch fixed costs show)\n\n"
+                f"`ncu --metrics gpu__time_duration.sum` around one eager step of `bench/profile_step.py {b}`. Compare with the\n"
+                "batch-256 list: a kernel whose time does not fall with the batch is latency-bound.\n\n```\n" + txt + "```\n")
 
 
 def ncu_reports():
