@@ -504,3 +504,24 @@ def test_model_parallel_demo_resnet_walks_through_on_cpu():
     assert out.returncode == 0, out.stderr[-2000:]
     assert out.stdout.count("25557032") == 2
     assert "naive: (8, 1000) pipelined (cut after layer2.1): (8, 1000)" in out.stdout
+
+
+def test_statistics_copy_count_and_switches_through_the_c_abi():
+    """Host-side policy of the BatchNorm partial sums (csrc/config.cu), reachable without a GPU: the copy count
+    falls with the channel count, deterministic mode uses one slot per CTA, the pre-zeroed switch round-trips."""
+    from pytorch_distributed_training_tutorials_b200 import _lib
+    L = _lib.lib()
+    was = _lib.is_deterministic()
+    try:
+        _lib.set_deterministic(False)
+        assert [L.b200dt_bn_replicas_used(c) for c in (8, 64, 128, 256, 512, 1024, 2048, 4096)] == [16, 16, 16, 8, 4, 2, 1, 1]
+        assert L.b200dt_bn_replicas() == 16
+        _lib.set_deterministic(True)
+        assert L.b200dt_bn_replicas() == 160 and L.b200dt_bn_replicas_used(2048) == 160
+    finally:
+        _lib.set_deterministic(was)
+    prev = L.b200dt_get_sums_prezeroed()
+    L.b200dt_set_sums_prezeroed(1)
+    assert L.b200dt_get_sums_prezeroed() == 1
+    L.b200dt_set_sums_prezeroed(prev)
+    assert L.b200dt_capture_id(None) == 0               # no capture (and no GPU here): 0, not an error
