@@ -25,7 +25,7 @@ keep = {"tc_gemm_kernel": "tc_gemm_kernel", "coll_kernelILi1ELi8": "coll_twoshot
         "stem_fprop_kernel": "stem_fprop_implicit", "stem_wgrad_kernel": "stem_wgrad_implicit",
         "p2p_multi_copy_kernel": "p2p_multi_copy", "bn_bwd_apply_kernelILi0": "bn_bwd_apply",
         "multi_opt_kernelILb1": "multi_adam", "splitk_fold_kernel": "splitk_fold", "ce_kernelIfLi1": "cross_entropy"}
-pats = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "SYNCS", "LDGMC", "STGMC", "ATOMG", "REDG", "HMMA", "ELECT", "UBLKCP", "ACQBULK", "PREEXIT"]
+pats = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "SYNCS", "LDGMC", "STGMC", "ATOMG", "REDG", "HMMA", "ELECT", "UBLKCP", "ACQBULK", "PREEXIT", "BRA.U.ANY"]
 rows = []
 for name, body in funcs.items():
     for key, short in keep.items():
@@ -34,7 +34,7 @@ for name, body in funcs.items():
     cnt = collections.Counter()
     for ins in body:
         for p in pats:
-            if re.search(r"\b" + p, ins):
+            if re.search(r"\b" + re.escape(p), ins):
                 cnt[p] += 1
     if cnt:
         rows.append((name, len(body), cnt))
@@ -42,7 +42,9 @@ md = ["# SASS mnemonics per kernel (cuobjdump -sass of _native/libb200dt.so, sm_
       "`UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,",
       "`UTMALDG` / `UTMASTG` / `UTMAREDG` = TMA load / store / reduce-add, `SYNCS` = mbarrier, `LDGMC` / `STGMC`-class =",
       "multimem (NVLS), `ATOMG...SYS` = system-scope flag CAS, `ACQBULK` / `PREEXIT` = griddepcontrol.wait / .launch_dependents",
-      "(programmatic dependent launch). No `HMMA` (legacy mma.sync) anywhere.", "",
+      "(programmatic dependent launch), `BRA.U.ANY` = back-edge of a waterfall loop around a uniform-datapath instruction",
+      "(tc_gemm_kernel had one per UTCHMMA / UTMALDG before its issuing warps ran converged with an elected lane).",
+      "No `HMMA` (legacy mma.sync) anywhere.", "",
       "| kernel | instructions | " + " | ".join(pats) + " |", "|---|---|" + "---|" * len(pats)]
 for name, n, cnt in sorted(rows, key=lambda r: -r[1]):
     md.append(f"| `{name[:70]}` | {n} | " + " | ".join(str(cnt.get(p, 0) or "") for p in pats) + " |")
